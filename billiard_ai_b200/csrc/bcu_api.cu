@@ -1,0 +1,442 @@
+// C-ABI layer of libbilliard_cuda.so (see include/billiard_cuda.h).  Host-side plumbing only:
+// derives the rail geometry the way the reference's Rail ctor does, owns device buffers, launches
+// the kernels of bcu_kernels.cu / bcu_topk.cu on one stream and copies results back.
+// There is no CPU path in this library.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/billiard_cuda.h"
+#include "bcu_kernels.cuh"
+
+using namespace bcu;
+
+namespace {
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct bcu_engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    std::string err;
+    TableGeom table;
+    RulesData rules;
+    std::vector<float> railDerived;
+    int maxCtas = 148;
+    int64_t launches = 0;
+    bool countersOn = false;
+
+    // states
+    int nStates = 0, nBalls = 0;
+    DevBuf<float> dStatePos;
+    DevBuf<int8_t> dStateType;
+    DevBuf<uint32_t> dExpected;
+    DevBuf<uint64_t> dStateBase;
+    bool hasStateBase = false;
+    // explicit candidates
+    DevBuf<int32_t> dCandState;
+    DevBuf<float> dVx, dVy;
+    DevBuf<uint64_t> dSearchCost, dBaseCost;
+    // grid
+    DevBuf<float> dDirs, dSpeeds;
+    // results
+    DevBuf<uint64_t> dCost;
+    DevBuf<uint32_t> dFlags, dPotted;
+    DevBuf<float> dFinalTime, dFinalPos;
+    DevBuf<int4> dEventLog;
+    DevBuf<float> dTraceTimes, dTraceRec;
+    DevBuf<unsigned long long> dCounters;
+    // top-k
+    DevBuf<unsigned char> dTopkScratch;
+    DevBuf<uint64_t> dTopCost, dTopId;
+    DevBuf<int32_t> dTopCount;
+    DevBuf<uint64_t> dGatherIds;
+    DevBuf<float> dGatherPos, dGatherTime;
+    DevBuf<uint32_t> dGatherPotted;
+
+    LaunchParams last{};
+    bool haveLast = false;
+    int64_t lastFirst = 0;
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            e->err = std::string(#call) + ": " + cudaGetErrorString(_e);                           \
+            return BCU_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+
+static int fail(bcu_engine* e, int code, const char* msg) {
+    if (e) e->err = msg;
+    return code;
+}
+
+// search::Rail ctor (reference type.cpp:56-72), binary32:
+//   normal = glm::normalize(perp(end - start)), perp(v) = (-v.y, v.x); shifted = p + shiftDirection * ballRadius
+static void derive_rail(const float* r6, float radius, RailGeom* g, float* derived6) {
+    const float sx = r6[0], sy = r6[1], ex = r6[2], ey = r6[3], hx = r6[4], hy = r6[5];
+    const float dx = ex - sx, dy = ey - sy;
+    const float px = -dy, py = dx;
+    const float tx = px * px, ty = py * py;
+    const float inv = 1.0f / std::sqrt(tx + ty);
+    const float nx = px * inv, ny = py * inv;
+    const float ssx = sx + hx * radius, ssy = sy + hy * radius;
+    const float sex = ex + hx * radius, sey = ey + hy * radius;
+    g->sx = ssx; g->sy = ssy;
+    g->dx = sex - ssx; g->dy = sey - ssy;  // billiard_physics.cpp:731-734: end - start, taken at each call
+    g->nx = nx; g->ny = ny;
+    derived6[0] = nx; derived6[1] = ny; derived6[2] = ssx; derived6[3] = ssy; derived6[4] = sex; derived6[5] = sey;
+}
+
+extern "C" {
+
+const char* bcu_version(void) { return "billiard_cuda 0.1 (sm_100a)"; }
+
+int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int device, bcu_engine** out) {
+    if (!out) return BCU_ERR_INVALID;
+    *out = nullptr;
+    if (!table || !rules || !table->rails || !table->pockets || !rules->score) return BCU_ERR_INVALID;
+    if (table->n_rails < 0 || table->n_rails > MAX_RAILS || table->n_pockets < 0 || table->n_pockets > MAX_POCKETS ||
+        rules->n_types < 1 || rules->n_types > MAX_TYPES)
+        return BCU_ERR_INVALID;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+        cudaGetLastError();
+        return BCU_ERR_NO_DEVICE;  // no CPU fallback
+    }
+    bcu_engine* e = new bcu_engine();
+    e->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete e; return BCU_ERR_NO_DEVICE; }
+    std::memset(&e->table, 0, sizeof(e->table));
+    std::memset(&e->rules, 0, sizeof(e->rules));
+    e->table.nRails = table->n_rails;
+    e->table.nPockets = table->n_pockets;
+    e->table.diameter = table->ball_radius * 2;  // util.cpp:65: conf._ball._diameter = ballRadius * 2
+    e->table.diameterSq = e->table.diameter * e->table.diameter;
+    e->railDerived.resize((size_t)table->n_rails * 6);
+    for (int i = 0; i < table->n_rails; ++i)
+        derive_rail(table->rails + 6 * i, table->ball_radius, &e->table.rails[i], &e->railDerived[6 * i]);
+    for (int i = 0; i < table->n_pockets; ++i) {
+        const float* p = table->pockets + 3 * i;
+        e->table.pockets[i].x = p[0]; e->table.pockets[i].y = p[1]; e->table.pockets[i].r = p[2];
+        e->table.pockets[i].r2 = p[2] * p[2];
+    }
+    e->rules.nTypes = rules->n_types;
+    e->rules.cueType = rules->cue_type;
+    for (int i = 0; i < rules->n_types; ++i) e->rules.score[i] = rules->score[i];
+    if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&e->evStart) != cudaSuccess || cudaEventCreate(&e->evStop) != cudaSuccess) {
+        delete e;
+        return BCU_ERR_CUDA;
+    }
+    upload_constants(e->table, e->rules, e->stream);
+    e->maxCtas = simulate_max_ctas(device);
+    if (cudaGetLastError() != cudaSuccess) { delete e; return BCU_ERR_CUDA; }
+    *out = e;
+    return BCU_OK;
+}
+
+void bcu_destroy(bcu_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    e->dStatePos.release(); e->dStateType.release(); e->dExpected.release(); e->dStateBase.release();
+    e->dCandState.release(); e->dVx.release(); e->dVy.release(); e->dSearchCost.release(); e->dBaseCost.release();
+    e->dDirs.release(); e->dSpeeds.release();
+    e->dCost.release(); e->dFlags.release(); e->dPotted.release(); e->dFinalTime.release(); e->dFinalPos.release();
+    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release();
+    e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
+    e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
+    if (e->evStart) cudaEventDestroy(e->evStart);
+    if (e->evStop) cudaEventDestroy(e->evStop);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+const char* bcu_last_error(const bcu_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+int bcu_get_rail_derived(const bcu_engine* e, float* out6) {
+    if (!e || !out6) return BCU_ERR_INVALID;
+    std::memcpy(out6, e->railDerived.data(), e->railDerived.size() * sizeof(float));
+    return BCU_OK;
+}
+
+int bcu_set_states(bcu_engine* e, int32_t nStates, int32_t nBalls, const float* pos, const int32_t* types,
+                   const uint32_t* expectedMask, const uint64_t* baseCost) {
+    if (!e) return BCU_ERR_INVALID;
+    if (nStates < 1 || nBalls < 1 || nBalls > MAX_BALLS || !pos || !types || !expectedMask)
+        return fail(e, BCU_ERR_INVALID, "bcu_set_states: bad arguments");
+    CK(cudaSetDevice(e->device));
+    const size_t nb = (size_t)nStates * nBalls;
+    std::vector<int8_t> t8(nb);
+    int cue = 0;
+    for (size_t i = 0; i < nb; ++i) {
+        if (types[i] >= e->rules.nTypes) return fail(e, BCU_ERR_INVALID, "bcu_set_states: type code out of range");
+        t8[i] = (int8_t)(types[i] < 0 ? -1 : types[i]);
+        cue += types[i] == e->rules.cueType;
+    }
+    CK(e->dStatePos.reserve(nb * 2));
+    CK(e->dStateType.reserve(nb));
+    CK(e->dExpected.reserve(nStates));
+    CK(cudaMemcpyAsync(e->dStatePos.p, pos, nb * 2 * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dStateType.p, t8.data(), nb, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dExpected.p, expectedMask, nStates * sizeof(uint32_t), cudaMemcpyHostToDevice, e->stream));
+    e->hasStateBase = baseCost != nullptr;
+    if (baseCost) {
+        CK(e->dStateBase.reserve(nStates));
+        CK(cudaMemcpyAsync(e->dStateBase.p, baseCost, nStates * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));  // t8 is a temporary
+    e->nStates = nStates;
+    e->nBalls = nBalls;
+    e->haveLast = false;
+    return BCU_OK;
+}
+
+static int reserve_results(bcu_engine* e, int64_t n, bool wantPos, bool wantLog) {
+    CK(e->dCost.reserve(n)); CK(e->dFlags.reserve(n)); CK(e->dPotted.reserve(n)); CK(e->dFinalTime.reserve(n));
+    if (wantPos) CK(e->dFinalPos.reserve((size_t)n * e->nBalls * 2));
+    if (wantLog) CK(e->dEventLog.reserve((size_t)n * 32));
+    CK(e->dCounters.reserve(8));
+    return BCU_OK;
+}
+
+static void fill_common(bcu_engine* e, LaunchParams& p, int64_t n, bool wantPos, bool wantLog) {
+    std::memset(&p, 0, sizeof(p));
+    p.nCand = n;
+    p.states.nStates = e->nStates; p.states.nBalls = e->nBalls;
+    p.states.pos = e->dStatePos.p; p.states.type = e->dStateType.p; p.states.expectedMask = e->dExpected.p;
+    p.out.cost = e->dCost.p; p.out.flags = e->dFlags.p; p.out.potted = e->dPotted.p; p.out.finalTime = e->dFinalTime.p;
+    p.out.finalPos = wantPos ? e->dFinalPos.p : nullptr;
+    p.out.eventLog = wantLog ? e->dEventLog.p : nullptr;
+    p.out.counters = e->countersOn ? e->dCounters.p : nullptr;
+}
+
+static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
+    if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
+    if (p.out.eventLog) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
+    CK(cudaEventRecord(e->evStart, e->stream));
+    CK(launch_simulate(p, trace, e->maxCtas, e->stream));
+    CK(cudaEventRecord(e->evStop, e->stream));
+    e->launches++;
+    return BCU_OK;
+}
+
+static int copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
+    if (!out) return BCU_OK;
+    if (out->cost) CK(cudaMemcpyAsync(out->cost, e->dCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+    if (out->flags) CK(cudaMemcpyAsync(out->flags, e->dFlags.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (out->potted) CK(cudaMemcpyAsync(out->potted, e->dPotted.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (out->final_time) CK(cudaMemcpyAsync(out->final_time, e->dFinalTime.p + offset, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (out->final_pos) {
+        if (!e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "final_pos was not produced by the last launch");
+        CK(cudaMemcpyAsync(out->final_pos, e->dFinalPos.p + (size_t)offset * e->nBalls * 2,
+                           (size_t)n * e->nBalls * 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    }
+    if (out->event_log) {
+        if (!e->last.out.eventLog) return fail(e, BCU_ERR_STATE, "event_log was not produced by the last launch");
+        CK(cudaMemcpyAsync(out->event_log, e->dEventLog.p + (size_t)offset * 32, (size_t)n * 32 * sizeof(int4),
+                           cudaMemcpyDeviceToHost, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float* vx, const float* vy,
+                 const uint64_t* searchCost, const uint64_t* baseCost, const bcu_results* out) {
+    if (!e) return BCU_ERR_INVALID;
+    if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate: call bcu_set_states first");
+    if (n < 0 || (n > 0 && (!stateIdx || !vx || !vy || !searchCost || !baseCost)))
+        return fail(e, BCU_ERR_INVALID, "bcu_evaluate: bad arguments");
+    if (n == 0) return BCU_OK;
+    for (int64_t i = 0; i < n; ++i)
+        if (stateIdx[i] < 0 || stateIdx[i] >= e->nStates) return fail(e, BCU_ERR_INVALID, "bcu_evaluate: state index out of range");
+    CK(cudaSetDevice(e->device));
+    CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n));
+    CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
+    const bool wantPos = out && out->final_pos, wantLog = out && out->event_log;
+    int rc = reserve_results(e, n, wantPos, wantLog);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(e->dCandState.p, stateIdx, n * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVx.p, vx, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVy.p, vy, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dSearchCost.p, searchCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dBaseCost.p, baseCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    LaunchParams p;
+    fill_common(e, p, n, wantPos, wantLog);
+    p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
+    p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
+    rc = run(e, p, false);
+    if (rc) return rc;
+    e->last = p; e->haveLast = true; e->lastFirst = 0;
+    return copy_back(e, 0, n, out);
+}
+
+int bcu_evaluate_grid(bcu_engine* e, int32_t nDirs, int32_t nSpeeds, const float* dirs, const float* speeds,
+                      uint64_t searchCost, int64_t first, int64_t count) {
+    if (!e) return BCU_ERR_INVALID;
+    if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate_grid: call bcu_set_states first");
+    if (nDirs < 1 || nSpeeds < 1 || !dirs || !speeds) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: bad arguments");
+    const int64_t total = (int64_t)e->nStates * nDirs * nSpeeds;
+    if (count < 0) count = total - first;
+    if (first < 0 || first + count > total) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: shard out of range");
+    CK(cudaSetDevice(e->device));
+    CK(e->dDirs.reserve((size_t)nDirs * 2)); CK(e->dSpeeds.reserve(nSpeeds));
+    CK(cudaMemcpyAsync(e->dDirs.p, dirs, (size_t)nDirs * 2 * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dSpeeds.p, speeds, nSpeeds * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    int rc = reserve_results(e, count, true, false);
+    if (rc) return rc;
+    LaunchParams p;
+    fill_common(e, p, count, true, false);
+    p.src.gridDirs = nDirs; p.src.gridSpeeds = nSpeeds; p.src.dirTable = e->dDirs.p; p.src.speedTable = e->dSpeeds.p;
+    p.src.gridSearchCost = searchCost;
+    p.src.stateBaseCost = e->hasStateBase ? e->dStateBase.p : nullptr;
+    p.src.firstCandidate = first;
+    rc = run(e, p, false);
+    if (rc) return rc;
+    e->last = p; e->haveLast = true; e->lastFirst = first;
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+int bcu_rerun(bcu_engine* e) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast) return fail(e, BCU_ERR_STATE, "bcu_rerun: nothing to re-run");
+    CK(cudaSetDevice(e->device));
+    int rc = run(e, e->last, false);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+int bcu_fetch_results(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast) return fail(e, BCU_ERR_STATE, "bcu_fetch_results: no launch yet");
+    if (offset < 0 || n < 0 || offset + n > e->last.nCand) return fail(e, BCU_ERR_INVALID, "bcu_fetch_results: range");
+    CK(cudaSetDevice(e->device));
+    return copy_back(e, offset, n, out);
+}
+
+int bcu_topk(bcu_engine* e, int32_t k, uint64_t* outCost, uint64_t* outId, int32_t* outCount) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast) return fail(e, BCU_ERR_STATE, "bcu_topk: no launch yet");
+    if (k < 1 || k > 1024 || !outCost || !outId || !outCount) return fail(e, BCU_ERR_INVALID, "bcu_topk: bad arguments");
+    CK(cudaSetDevice(e->device));
+    const int64_t n = e->last.nCand;
+    const size_t sb = topk_scratch_bytes(n, k);
+    CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
+    CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
+                   e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
+    e->launches += 2;
+    int32_t valid = 0;
+    CK(cudaMemcpyAsync(outCost, e->dTopCost.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(outId, e->dTopId.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(&valid, e->dTopCount.p, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    *outCount = valid < k ? valid : k;
+    return BCU_OK;
+}
+
+int bcu_simulate_trace(bcu_engine* e, int32_t nBalls, const float* pos, const int32_t* types, float vx, float vy,
+                       int32_t* outLayers, float* outTimes, float* outRec) {
+    if (!e || !pos || !types || !outLayers || !outTimes || !outRec) return BCU_ERR_INVALID;
+    const uint32_t expected = 0xffffffffu;
+    int rc = bcu_set_states(e, 1, nBalls, pos, types, &expected, nullptr);
+    if (rc) return rc;
+    const int32_t s0 = 0;
+    const uint64_t sc = 0, bc = 0;
+    CK(e->dCandState.reserve(1)); CK(e->dVx.reserve(1)); CK(e->dVy.reserve(1)); CK(e->dSearchCost.reserve(1)); CK(e->dBaseCost.reserve(1));
+    rc = reserve_results(e, 1, true, false);
+    if (rc) return rc;
+    CK(e->dTraceTimes.reserve(BCU_MAX_LAYERS)); CK(e->dTraceRec.reserve((size_t)BCU_MAX_LAYERS * nBalls * BCU_TRACE_REC));
+    CK(cudaMemcpyAsync(e->dCandState.p, &s0, sizeof(s0), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVx.p, &vx, sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVy.p, &vy, sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dSearchCost.p, &sc, sizeof(sc), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dBaseCost.p, &bc, sizeof(bc), cudaMemcpyHostToDevice, e->stream));
+    LaunchParams p;
+    fill_common(e, p, 1, true, false);
+    p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
+    p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
+    p.out.traceTimes = e->dTraceTimes.p; p.out.traceRec = e->dTraceRec.p;
+    rc = run(e, p, true);
+    if (rc) return rc;
+    uint32_t flags = 0;
+    CK(cudaMemcpyAsync(&flags, e->dFlags.p, sizeof(flags), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(outTimes, e->dTraceTimes.p, BCU_MAX_LAYERS * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(outRec, e->dTraceRec.p, (size_t)BCU_MAX_LAYERS * nBalls * BCU_TRACE_REC * sizeof(float),
+                       cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->haveLast = false;
+    *outLayers = (flags & BCU_F_COMPLETED) ? (int32_t)BCU_N_EVENTS(flags) + 1 : 0;
+    return BCU_OK;
+}
+
+int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* outPos, uint32_t* outPotted, float* outTime) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast || !e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "bcu_gather: no launch with final positions");
+    if (n < 0 || (n > 0 && !ids)) return fail(e, BCU_ERR_INVALID, "bcu_gather: bad arguments");
+    CK(cudaSetDevice(e->device));
+    // few (<= 1024) records: one small copy per record keeps this path kernel-free
+    const int NB = e->nBalls;
+    for (int32_t i = 0; i < n; ++i) {
+        const int64_t local = (int64_t)ids[i] - e->lastFirst;
+        if (local < 0 || local >= e->last.nCand) return fail(e, BCU_ERR_INVALID, "bcu_gather: id not in the last launch");
+        if (outPos) CK(cudaMemcpyAsync(outPos + (size_t)i * NB * 2, e->dFinalPos.p + (size_t)local * NB * 2, NB * 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+        if (outPotted) CK(cudaMemcpyAsync(outPotted + i, e->dPotted.p + local, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+        if (outTime) CK(cudaMemcpyAsync(outTime + i, e->dFinalTime.p + local, sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    }
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+int bcu_last_kernel_ms(bcu_engine* e, float* outMs) {
+    if (!e || !outMs) return BCU_ERR_INVALID;
+    CK(cudaEventSynchronize(e->evStop));
+    CK(cudaEventElapsedTime(outMs, e->evStart, e->evStop));
+    return BCU_OK;
+}
+
+int bcu_enable_counters(bcu_engine* e, int enable) {
+    if (!e) return BCU_ERR_INVALID;
+    e->countersOn = enable != 0;
+    if (e->haveLast) e->last.out.counters = e->countersOn ? e->dCounters.p : nullptr;
+    return BCU_OK;
+}
+
+int bcu_get_counters(bcu_engine* e, uint64_t* out5) {
+    if (!e || !out5) return BCU_ERR_INVALID;
+    if (!e->dCounters.p) return fail(e, BCU_ERR_STATE, "bcu_get_counters: no launch yet");
+    unsigned long long h[8];
+    CK(cudaMemcpyAsync(h, e->dCounters.p, sizeof(h), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    for (int i = 0; i < 5; ++i) out5[i] = h[i];
+    return BCU_OK;
+}
+
+int64_t bcu_launch_count(const bcu_engine* e) { return e ? e->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,65 @@
+// Kernel-side parameter blocks shared between bcu_kernels.cu and the C-ABI layer (bcu_api.cu).
+#pragma once
+
+#include "bcu_common.cuh"
+
+namespace bcu {
+
+// Where a launch takes its candidates from.
+struct CandidateSource {
+    // explicit candidates (SoA, device pointers); used when gridDirs == 0
+    const int32_t* stateIdx;
+    const float* vx;
+    const float* vy;
+    const uint64_t* searchCost;
+    const uint64_t* baseCost;
+    // direction x speed grid per beam state; used when gridDirs > 0:
+    //   candidate c -> state s = c / (gridDirs*gridSpeeds), dir k = (c / gridSpeeds) % gridDirs, speed j = c % gridSpeeds
+    //   velocity = speedTable[j] * (dirTable[2k], dirTable[2k+1])  (one float multiply per component)
+    int32_t gridDirs, gridSpeeds;
+    const float* dirTable;     // [gridDirs][2] unit vectors, computed on the host
+    const float* speedTable;   // [gridSpeeds]
+    uint64_t gridSearchCost;   // constant searchCost of synthetic candidates
+    const uint64_t* stateBaseCost;  // [nStates] accumulated cost of the beam state (may be null = 0)
+    int64_t firstCandidate;    // global id of this launch's first candidate (multi-GPU shards)
+};
+
+struct StateTable {
+    int32_t nStates, nBalls;
+    const float* pos;             // [nStates][nBalls][2]
+    const int8_t* type;           // [nStates][nBalls], -1 = absent
+    const uint32_t* expectedMask; // [nStates] bit t = type t is a legal pot
+};
+
+struct Results {
+    uint64_t* cost;       // baseCost + simulationCost, ~0 when not COMPLETED
+    uint32_t* flags;      // ResultFlags | nEvents << 8
+    uint32_t* potted;     // bit b = ball b potted at the end
+    float* finalTime;
+    float* finalPos;      // [nCand][nBalls][2]  (may be null)
+    int4* eventLog;       // [nCand][32] {type, a, b, layer time bits} (may be null)
+    // single-candidate trace (bcu_simulate_trace): per layer, per ball 10 floats as oracle/ref_driver.cpp
+    float* traceTimes;    // [32]
+    float* traceRec;      // [32][nBalls][10]
+    // work counters (may be null): [0] events [1] pair items [2] quartics [3] rail items [4] pocket items
+    unsigned long long* counters;
+};
+
+struct LaunchParams {
+    int64_t nCand;
+    CandidateSource src;
+    StateTable states;
+    Results out;
+};
+
+void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
+cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, cudaStream_t stream);
+int simulate_max_ctas(int device);
+
+// top-k selection on (cost, candidate id) among VALID candidates; see bcu_topk.cu
+cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCand, int64_t firstCandidate, int k,
+                        uint64_t* outKeyCost, uint64_t* outKeyId, int32_t* outCount, void* scratch, size_t scratchBytes,
+                        cudaStream_t stream);
+size_t topk_scratch_bytes(int64_t nCand, int k);
+
+}  // namespace bcu

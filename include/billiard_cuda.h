@@ -1,0 +1,139 @@
+/*
+ * billiard_cuda.h -- thin C ABI of the B200 strike-evaluation engine (libbilliard_cuda.so).
+ *
+ * This is the drop-in boundary below the reference's C++ entry points
+ *     billiard::search::simulate(State, vec2, Configuration)      lib/billiard_search/include/billiard_search/billiard_search.hpp:17-18
+ *     billiard::search::search(State, Search, solutions, Config)  lib/billiard_search/include/billiard_search/billiard_search.hpp:9-12
+ * whose hot loop (billiard_search.cpp:1358-1471 simulate, :1550-1573 nextEvent, :1957-1992 createLayer,
+ * :1473-1532 simulationCost, rules billiard_snooker.cpp:787-790, 1128-1153) it replaces.
+ * The C++ mirror of those entry points that calls this ABI lives in billiard_ai_b200/host/.
+ *
+ * Conventions: POD only, caller-owned buffers, no globals, one CUDA stream per engine, every call
+ * returns a bcu_status (0 = OK).  There is NO CPU fallback: if no CUDA device is usable,
+ * bcu_create fails with BCU_ERR_NO_DEVICE.
+ */
+#ifndef BILLIARD_CUDA_H
+#define BILLIARD_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BCU_MAX_BALLS 32
+#define BCU_MAX_RAILS 32
+#define BCU_MAX_POCKETS 8
+#define BCU_MAX_TYPES 16
+#define BCU_MAX_LAYERS 32 /* MAX_EVENTS (30) + the input layer, rounded up; billiard_search.cpp:20 */
+#define BCU_TRACE_REC 10
+
+typedef enum {
+    BCU_OK = 0,
+    BCU_ERR_NO_DEVICE = 1,   /* no CUDA device / driver: there is no CPU fallback */
+    BCU_ERR_INVALID = 2,     /* bad argument */
+    BCU_ERR_CUDA = 3,        /* a CUDA runtime call failed; see bcu_last_error */
+    BCU_ERR_STATE = 4        /* call sequence error (e.g. evaluate before set_states) */
+} bcu_status;
+
+/* result flags, per candidate (low byte of bcu_results.flags; bits 8..15 = number of events) */
+#define BCU_F_COMPLETED 1u /* all balls at rest / potted within MAX_EVENTS                         */
+#define BCU_F_VALID 2u     /* rules: valid end state (billiard_snooker.cpp:1128-1153)              */
+#define BCU_F_OVERFLOW 4u  /* > MAX_EVENTS events: the reference discards it (billiard_search.cpp:1376-1379) */
+#define BCU_F_NOEVENT 8u   /* no next event found (billiard_search.cpp:1464-1467)                  */
+#define BCU_N_EVENTS(flags) (((flags) >> 8) & 0xffu)
+
+/* node kinds in traces == billiard::search::node::NodeType (type.hpp:167-180) */
+/* event types in logs  == billiard::search::event::EventType (type.hpp:87-98)  */
+
+typedef struct bcu_engine bcu_engine;
+
+/* Table geometry: what search::Configuration::_table/_ball hold (type.hpp:301-322).
+ * rails: n_rails x {start.x, start.y, end.x, end.y, shiftDirection.x, shiftDirection.y} -- the Rail ctor
+ * arguments (type.hpp:69-71); normal and shifted end points are derived as type.cpp:56-72 does.
+ * pockets: n_pockets x {position.x, position.y, radius} (type.hpp:46-55). */
+typedef struct {
+    int32_t n_rails;
+    int32_t n_pockets;
+    float ball_radius;
+    const float* rails;
+    const float* pockets;
+} bcu_table_desc;
+
+/* Rules as data (the reference's std::function rules, type.hpp:324-332, cannot run on a device):
+ * score[t] = _scoreForPottedBall(type t); cue_type = type code of "WHITE".
+ * Valid end state = billiard::snooker::validEndState with the per-state expected-type mask. */
+typedef struct {
+    int32_t n_types;
+    int32_t cue_type;
+    const double* score;
+} bcu_rules_desc;
+
+/* Host result buffers; any pointer may be NULL (that output is then not copied back). */
+typedef struct {
+    uint64_t* cost;      /* [n] parent cost + simulationCost; UINT64_MAX when not COMPLETED */
+    uint32_t* flags;     /* [n] */
+    uint32_t* potted;    /* [n] bit b: ball b is potted in the final layer */
+    float* final_time;   /* [n] time of the final layer */
+    float* final_pos;    /* [n][n_balls][2] */
+    int32_t* event_log;  /* [n][32][4] {event type, ball a, ball b | rail | pocket, layer time bits}, -1 padded */
+} bcu_results;
+
+/* ---- lifecycle ---------------------------------------------------------------------------------- */
+int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int device, bcu_engine** out);
+void bcu_destroy(bcu_engine* e);
+const char* bcu_last_error(const bcu_engine* e);
+const char* bcu_version(void);
+/* derived rail geometry as uploaded: n_rails x {normal.xy, shiftedStart.xy, shiftedEnd.xy} */
+int bcu_get_rail_derived(const bcu_engine* e, float* out6);
+
+/* ---- table states (the beam) ------------------------------------------------------------------------
+ * pos [n_states][n_balls][2]; types [n_states][n_balls] (type code, -1 = no ball);
+ * expected_mask [n_states] (bit t: potting type t is legal = the Search::_types of that state);
+ * base_cost [n_states] accumulated cost of the state's parent chain (may be NULL = 0). */
+int bcu_set_states(bcu_engine* e, int32_t n_states, int32_t n_balls, const float* pos, const int32_t* types,
+                   const uint32_t* expected_mask, const uint64_t* base_cost);
+
+/* ---- evaluation of explicit candidates (reference: one SIMULATION node each, billiard_search.cpp:797-826) --
+ * Host buffers; host->device and device->host copies are part of the call. */
+int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* state_idx, const float* vx, const float* vy,
+                 const uint64_t* search_cost, const uint64_t* base_cost, const bcu_results* out);
+
+/* ---- evaluation of a direction x speed grid per state (synthetic configs 2-5) -------------
+ * candidate id c = (state * n_dirs + dir) * n_speeds + speed; velocity = speeds[speed] * dirs[dir].
+ * dirs [n_dirs][2] unit vectors and speeds [n_speeds] are host arrays (uploaded once per call).
+ * Candidates [first, first+count) are evaluated (count < 0: all) -- the multi-GPU shard of this rank.
+ * Results stay on the device; fetch them with bcu_fetch_results / bcu_topk. */
+int bcu_evaluate_grid(bcu_engine* e, int32_t n_dirs, int32_t n_speeds, const float* dirs, const float* speeds,
+                      uint64_t search_cost, int64_t first, int64_t count);
+/* Re-run the last bcu_evaluate_grid launch with everything already resident (timing loops). */
+int bcu_rerun(bcu_engine* e);
+/* Copy results of the last launch (device -> host). */
+int bcu_fetch_results(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out);
+
+/* ---- block-level top-k on (cost, candidate id) among VALID candidates of the last launch ------------
+ * out_cost/out_id [k] ascending; *out_count = number of valid entries written (<= k). */
+int bcu_topk(bcu_engine* e, int32_t k, uint64_t* out_cost, uint64_t* out_id, int32_t* out_count);
+/* Final positions / potted mask of selected candidates of the last launch (ids are global ids). */
+int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* out_pos, uint32_t* out_potted, float* out_time);
+
+/* ---- single strike with the full layer trace (reference public simulate(), billiard_search.cpp:141-175) --
+ * pos [n_balls][2], types [n_balls]; out_times [32]; out_rec [32][n_balls][10]:
+ *   {node kind, after.pos.xy, after.vel.xy, after.isRolling, before.vel.xy, cause index, -1}
+ * *out_layers = number of layers, 0 when the reference would return nullopt. */
+int bcu_simulate_trace(bcu_engine* e, int32_t n_balls, const float* pos, const int32_t* types, float vx, float vy,
+                       int32_t* out_layers, float* out_times, float* out_rec);
+
+/* ---- measurement hooks -------------------------------------------------------------------------------- */
+/* ms of the last kernel launch (CUDA events on the engine's stream) */
+int bcu_last_kernel_ms(bcu_engine* e, float* out_ms);
+/* work counters of the last launch when enabled: {events, pair items, quartics, rail items, pocket items} */
+int bcu_enable_counters(bcu_engine* e, int enable);
+int bcu_get_counters(bcu_engine* e, uint64_t* out5);
+/* number of kernels launched by this engine so far */
+int64_t bcu_launch_count(const bcu_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BILLIARD_CUDA_H */
