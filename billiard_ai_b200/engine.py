@@ -1,0 +1,245 @@
+"""ctypes binding of libbilliard_cuda.so (include/billiard_cuda.h).
+
+Host-side mirror of the reference's evaluation entry points for this path:
+  Engine.simulate_trace  <->  billiard::search::simulate(State, vec2, Configuration)   billiard_search.cpp:141-175
+  Engine.evaluate        <->  one SIMULATION node per candidate: simulate(node, state)  billiard_search.cpp:1358-1471
+                              + simulationCost (:1473-1532) + rules validEndState (billiard_snooker.cpp:1128-1153)
+  Engine.evaluate_grid / topk / gather  <->  one break level of the search (expand + best-first pop order,
+                              process.hpp:19-25) over a synthetic direction x speed grid
+
+There is no CPU path: a missing library or a missing CUDA device raises BcuError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libbilliard_cuda.so")
+
+F_COMPLETED, F_VALID, F_OVERFLOW, F_NOEVENT = 1, 2, 4, 8
+MAX_LAYERS = 32
+TRACE_REC = 10
+
+_STATUS = {1: "BCU_ERR_NO_DEVICE", 2: "BCU_ERR_INVALID", 3: "BCU_ERR_CUDA", 4: "BCU_ERR_STATE"}
+
+
+class BcuError(RuntimeError):
+    pass
+
+
+class _TableDesc(C.Structure):
+    _fields_ = [("n_rails", C.c_int32), ("n_pockets", C.c_int32), ("ball_radius", C.c_float),
+                ("rails", C.POINTER(C.c_float)), ("pockets", C.POINTER(C.c_float))]
+
+
+class _RulesDesc(C.Structure):
+    _fields_ = [("n_types", C.c_int32), ("cue_type", C.c_int32), ("score", C.POINTER(C.c_double))]
+
+
+class _Results(C.Structure):
+    _fields_ = [("cost", C.POINTER(C.c_uint64)), ("flags", C.POINTER(C.c_uint32)), ("potted", C.POINTER(C.c_uint32)),
+                ("final_time", C.POINTER(C.c_float)), ("final_pos", C.POINTER(C.c_float)),
+                ("event_log", C.POINTER(C.c_int32))]
+
+
+_lib = None
+
+
+def load_library(path=None):
+    """Loads libbilliard_cuda.so; raises BcuError when it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise BcuError(f"{p} is missing: build it with `python -m billiard_ai_b200.build` "
+                       "(this package has no CPU path)")
+    lib = C.CDLL(p)
+    lib.bcu_version.restype = C.c_char_p
+    lib.bcu_last_error.restype = C.c_char_p
+    lib.bcu_last_error.argtypes = [C.c_void_p]
+    lib.bcu_launch_count.restype = C.c_int64
+    lib.bcu_launch_count.argtypes = [C.c_void_p]
+    lib.bcu_destroy.argtypes = [C.c_void_p]
+    lib.bcu_destroy.restype = None
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def _null(t):
+    return C.POINTER(t)()
+
+
+class Engine:
+    """One engine = one CUDA device + one stream + the table / rules constants."""
+
+    def __init__(self, rails6, pockets3, ball_radius, scores, cue_type=0, device=0):
+        self.lib = load_library()
+        self._rails = np.ascontiguousarray(rails6, dtype=np.float32)
+        self._pockets = np.ascontiguousarray(np.asarray(pockets3, dtype=np.float32)[:, :3])
+        self._scores = np.ascontiguousarray(scores, dtype=np.float64)
+        td = _TableDesc(len(self._rails), len(self._pockets), C.c_float(np.float32(ball_radius)),
+                        _p(self._rails, C.c_float), _p(self._pockets, C.c_float))
+        rd = _RulesDesc(len(self._scores), int(cue_type), _p(self._scores, C.c_double))
+        h = C.c_void_p()
+        rc = self.lib.bcu_create(C.byref(td), C.byref(rd), C.c_int(device), C.byref(h))
+        if rc != 0:
+            raise BcuError(f"bcu_create failed: {_STATUS.get(rc, rc)} (no CPU fallback)")
+        self.h = h
+        self.n_rails = len(self._rails)
+        self.n_balls = 0
+        self.n_states = 0
+        self._last_n = 0
+
+    @classmethod
+    def from_table(cls, tbl, scores, cue_type=0, device=0):
+        """tbl: dict in the layout of tests/golden/table.json (reference configuration.json)."""
+        rails6 = np.array([[r["start"][0], r["start"][1], r["end"][0], r["end"][1], r["shift"][0], r["shift"][1]]
+                           for r in tbl["rails"]], dtype=np.float32)
+        pockets3 = np.array([[p["position"][0], p["position"][1], p["radius"]] for p in tbl["pockets"]],
+                            dtype=np.float32)
+        return cls(rails6, pockets3, tbl["ballRadius"], scores, cue_type, device)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.bcu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            msg = self.lib.bcu_last_error(self.h)
+            raise BcuError(f"{what}: {_STATUS.get(rc, rc)}: {msg.decode() if msg else ''}")
+
+    # ---- table ----------------------------------------------------------------------------------
+    def rail_derived(self):
+        out = np.zeros((self.n_rails, 6), dtype=np.float32)
+        self._ck(self.lib.bcu_get_rail_derived(self.h, _p(out, C.c_float)), "bcu_get_rail_derived")
+        return out
+
+    # ---- states ---------------------------------------------------------------------------------
+    def set_states(self, pos, types, expected_mask, base_cost=None):
+        pos = np.ascontiguousarray(pos, dtype=np.float32)
+        types = np.ascontiguousarray(types, dtype=np.int32)
+        if types.ndim == 1:
+            types = types[None]
+            pos = pos[None]
+        ns, nb = types.shape
+        em = np.ascontiguousarray(np.broadcast_to(np.asarray(expected_mask, dtype=np.uint32), (ns,)))
+        bc = None if base_cost is None else np.ascontiguousarray(
+            np.broadcast_to(np.asarray(base_cost, dtype=np.uint64), (ns,)))
+        self._ck(self.lib.bcu_set_states(self.h, C.c_int32(ns), C.c_int32(nb), _p(pos, C.c_float), _p(types, C.c_int32),
+                                         _p(em, C.c_uint32), _p(bc, C.c_uint64) if bc is not None else _null(C.c_uint64)),
+                 "bcu_set_states")
+        self.n_states, self.n_balls = ns, nb
+
+    # ---- explicit candidates ----------------------------------------------------------------------
+    def _result_buffers(self, n, final_pos, event_log):
+        out = dict(cost=np.zeros(n, np.uint64), flags=np.zeros(n, np.uint32), potted=np.zeros(n, np.uint32),
+                   final_time=np.zeros(n, np.float32),
+                   final_pos=np.zeros((n, self.n_balls, 2), np.float32) if final_pos else None,
+                   event_log=np.full((n, 32, 4), -1, np.int32) if event_log else None)
+        res = _Results(_p(out["cost"], C.c_uint64), _p(out["flags"], C.c_uint32), _p(out["potted"], C.c_uint32),
+                       _p(out["final_time"], C.c_float),
+                       _p(out["final_pos"], C.c_float) if final_pos else _null(C.c_float),
+                       _p(out["event_log"], C.c_int32) if event_log else _null(C.c_int32))
+        return out, res
+
+    @staticmethod
+    def _finish(out):
+        out["n_events"] = ((out["flags"] >> 8) & 0xff).astype(np.int32)
+        out["flags"] = out["flags"] & 0xff
+        return out
+
+    def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False):
+        vx = np.ascontiguousarray(vx, dtype=np.float32)
+        vy = np.ascontiguousarray(vy, dtype=np.float32)
+        n = len(vx)
+        cs = np.ascontiguousarray(np.broadcast_to(np.asarray(cand_state, dtype=np.int32), (n,)))
+        sc = np.ascontiguousarray(np.broadcast_to(np.asarray(search_cost, dtype=np.uint64), (n,)))
+        bc = np.ascontiguousarray(np.broadcast_to(np.asarray(base_cost, dtype=np.uint64), (n,)))
+        out, res = self._result_buffers(n, final_pos, event_log)
+        self._ck(self.lib.bcu_evaluate(self.h, C.c_int64(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
+                                       _p(sc, C.c_uint64), _p(bc, C.c_uint64), C.byref(res)), "bcu_evaluate")
+        self._last_n = n
+        return self._finish(out)
+
+    # ---- direction x speed grid -------------------------------------------------------------------
+    def evaluate_grid(self, dirs, speeds, search_cost=100000, first=0, count=-1):
+        dirs = np.ascontiguousarray(dirs, dtype=np.float32)
+        speeds = np.ascontiguousarray(speeds, dtype=np.float32)
+        total = self.n_states * len(dirs) * len(speeds)
+        self._ck(self.lib.bcu_evaluate_grid(self.h, C.c_int32(len(dirs)), C.c_int32(len(speeds)), _p(dirs, C.c_float),
+                                            _p(speeds, C.c_float), C.c_uint64(search_cost), C.c_int64(first),
+                                            C.c_int64(count)), "bcu_evaluate_grid")
+        self._last_n = total - first if count < 0 else count
+        return self._last_n
+
+    def rerun(self):
+        self._ck(self.lib.bcu_rerun(self.h), "bcu_rerun")
+
+    def fetch(self, offset=0, n=None, final_pos=True):
+        n = self._last_n - offset if n is None else n
+        out, res = self._result_buffers(n, final_pos, False)
+        self._ck(self.lib.bcu_fetch_results(self.h, C.c_int64(offset), C.c_int64(n), C.byref(res)), "bcu_fetch_results")
+        return self._finish(out)
+
+    def topk(self, k):
+        cost = np.zeros(k, np.uint64)
+        ids = np.zeros(k, np.uint64)
+        cnt = C.c_int32(0)
+        self._ck(self.lib.bcu_topk(self.h, C.c_int32(k), _p(cost, C.c_uint64), _p(ids, C.c_uint64), C.byref(cnt)),
+                 "bcu_topk")
+        return cost[:cnt.value], ids[:cnt.value]
+
+    def gather(self, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        n = len(ids)
+        pos = np.zeros((n, self.n_balls, 2), np.float32)
+        potted = np.zeros(n, np.uint32)
+        tm = np.zeros(n, np.float32)
+        self._ck(self.lib.bcu_gather(self.h, C.c_int32(n), _p(ids, C.c_uint64), _p(pos, C.c_float),
+                                     _p(potted, C.c_uint32), _p(tm, C.c_float)), "bcu_gather")
+        return pos, potted, tm
+
+    # ---- single strike with layer trace -------------------------------------------------------------
+    def simulate_trace(self, pos, types, vx, vy):
+        pos = np.ascontiguousarray(pos, dtype=np.float32)
+        types = np.ascontiguousarray(types, dtype=np.int32)
+        n = len(types)
+        times = np.zeros(MAX_LAYERS, np.float32)
+        rec = np.zeros((MAX_LAYERS, n, TRACE_REC), np.float32)
+        nl = C.c_int32(0)
+        self._ck(self.lib.bcu_simulate_trace(self.h, C.c_int32(n), _p(pos, C.c_float), _p(types, C.c_int32),
+                                             C.c_float(vx), C.c_float(vy), C.byref(nl), _p(times, C.c_float),
+                                             _p(rec, C.c_float)), "bcu_simulate_trace")
+        self.n_states, self.n_balls = 1, n
+        return nl.value, times[:nl.value], rec[:nl.value]
+
+    # ---- measurement hooks ------------------------------------------------------------------------
+    def last_kernel_ms(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.bcu_last_kernel_ms(self.h, C.byref(ms)), "bcu_last_kernel_ms")
+        return ms.value
+
+    def enable_counters(self, on=True):
+        self._ck(self.lib.bcu_enable_counters(self.h, C.c_int(int(on))), "bcu_enable_counters")
+
+    def counters(self):
+        out = np.zeros(5, np.uint64)
+        self._ck(self.lib.bcu_get_counters(self.h, _p(out, C.c_uint64)), "bcu_get_counters")
+        return dict(zip(["events", "pair_items", "quartics", "rail_items", "pocket_items"], out.tolist()))
+
+    def launch_count(self):
+        return int(self.lib.bcu_launch_count(self.h))

@@ -1,0 +1,262 @@
+"""GPU parity tests: the CUDA engine, called through the C ABI (include/billiard_cuda.h), against the oracles.
+
+Run on the B200 box:  python -m pytest tests -m gpu -x -q
+Nothing here reads /root/reference: the oracles are the prebuilt oracle/_ref/*.so (the port can be rebuilt from
+oracle/port on the box) and the committed fixtures under tests/golden/.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import GOLDEN, TYPE_CODE, SNOOKER_SCORES, F_COMPLETED, F_VALID
+from parity import compare_batch, summary, rel_close
+
+pytestmark = pytest.mark.gpu
+
+# Fraction of tie-free candidates that must agree with the oracle under the north_star rules.
+# 1.0 = every candidate.  See DESIGN.md "Parity status" for what the residual (if any) is.
+MIN_PARITY = float(os.environ.get("BCU_MIN_PARITY", "1.0"))
+
+
+@pytest.fixture(scope="module")
+def engine(table):
+    from billiard_ai_b200 import Engine
+    e = Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+    yield e
+    e.close()
+
+
+def _rand_layout(rng, n):
+    pos = []
+    while len(pos) < n:
+        p = np.array([rng.uniform(-880, 880), rng.uniform(-420, 420)], dtype=np.float32)
+        if all(np.hypot(*(p - q)) > 53.3 for q in pos):
+            pos.append(p)
+    return np.array(pos, dtype=np.float32)
+
+
+def test_native_library_is_loaded(engine):
+    import billiard_ai_b200
+    assert os.path.exists(billiard_ai_b200.LIB_PATH)
+    with open("/proc/self/maps") as f:
+        assert "libbilliard_cuda.so" in f.read()
+    assert b"sm_100a" in engine.lib.bcu_version()
+
+
+def test_rail_geometry_matches_reference_ctor(engine, table):
+    # golden railsDerived were produced by the reference's Rail ctor (type.cpp:56-72) via oracle/_ref
+    want = np.array(table["railsDerived"], dtype=np.float32)
+    got = engine.rail_derived()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def _shots():
+    with open(os.path.join(GOLDEN, "filmed_shots.json")) as f:
+        return json.load(f)["tests"]
+
+
+@pytest.mark.parametrize("shot", [s for s in _shots() if s["enabled"]], ids=lambda s: s["name"])
+def test_filmed_shot_structure_and_trace(engine, port, shot):
+    """Layer counts / node kinds asserted by test/billiard_search/src/simulation_vs_reality.cpp, and the full
+    per-layer trace against the oracle."""
+    pos = np.array([b["position"] for b in shot["balls"]], dtype=np.float32)
+    types = np.array([TYPE_CODE[b["type"]] for b in shot["balls"]], dtype=np.int32)
+    nl, times, rec = engine.simulate_trace(pos, types, *shot["velocity"])
+    if shot["expectedLayers"]:
+        assert nl in shot["expectedLayers"]
+    var_index = {b["var"]: i for i, b in enumerate(shot["balls"])}
+    for e in shot["expects"]:
+        if e.get("onlyIfLayers", nl) != nl or e.get("notIfLayers", -1) == nl or e["layer"] >= nl:
+            continue
+        r = rec[e["layer"], var_index[e["ball"]]]
+        assert int(r[0]) == e["kind"], (shot["name"], e)
+        if "afterRolling" in e:
+            assert bool(r[5]) == e["afterRolling"]
+    nl_p, t_p, rec_p, gap = port.simulate_trace(pos, types, *shot["velocity"])
+    if gap >= 1e-9:
+        assert nl == nl_p
+        assert rel_close(times, t_p).all()
+        assert np.array_equal(rec[..., 0], rec_p[..., 0]) and np.array_equal(rec[..., 8], rec_p[..., 8])
+        assert rel_close(rec[..., 1:3], rec_p[..., 1:3], scale=1881.0).all()
+        vs = np.maximum(np.abs(rec_p[..., 3:5]).max(), 1.0)
+        assert rel_close(rec[..., 3:5], rec_p[..., 3:5], scale=vs).all()
+        assert rel_close(rec[..., 6:8], rec_p[..., 6:8], scale=vs).all()
+
+
+def test_committed_reference_vectors(engine):
+    """tests/golden/ref_vectors.npz rand16_*: outputs of the reference itself (oracle/_ref) on seeded inputs."""
+    g = np.load(os.path.join(GOLDEN, "ref_vectors.npz"))
+    engine.set_states(g["rand16_pos"], g["rand16_types"], 1 << TYPE_CODE["RED"])
+    out = engine.evaluate(0, g["rand16_vx"], g["rand16_vy"], 100000, 0, final_pos=True, event_log=True)
+    ora = {k: g["rand16_" + k] for k in ("cost", "flags", "n_events", "potted", "final_time", "final_pos", "event_log")}
+    c = compare_batch(out, ora)
+    print(summary(c))
+    assert c["n_ok"] >= MIN_PARITY * c["n_clean"] - 12  # the golden file has no tie information: allow its ~2% near-ties
+
+
+@pytest.mark.parametrize("name", ["test_01", "situation1", "situation2"])
+@pytest.mark.parametrize("vm", [0, 1])
+def test_reference_planner_candidates_and_thesis_costs(engine, name, vm):
+    """Config 1: the reference planner's own candidate list (golden, from oracle/_ref ref_plan) evaluated on the
+    GPU must give the reference's solution costs -- incl. the totals printed in the thesis (72206, ...)."""
+    g = np.load(os.path.join(GOLDEN, "ref_vectors.npz"))
+    with open(os.path.join(GOLDEN, "layouts.json")) as f:
+        lay = json.load(f)[name]
+    pos = np.array([b["position"] for b in lay["balls"]], dtype=np.float32)
+    types = np.array([TYPE_CODE[b["type"]] for b in lay["balls"]], dtype=np.int32)
+    p = f"plan_{name}_vm{vm}_"
+    expected = 0
+    for t in lay.get("searchTypes", ["RED"]):
+        expected |= 1 << TYPE_CODE[t]
+    engine.set_states(pos, types, expected)
+    out = engine.evaluate(0, g[p + "vx"], g[p + "vy"], g[p + "search_cost"], g[p + "base_cost"], final_pos=False)
+    none = np.uint64(2**64 - 1)
+    want = g[p + "result_cost"]
+    is_solution = (out["flags"] & (F_COMPLETED | F_VALID)) == (F_COMPLETED | F_VALID)
+    got = np.where(is_solution, out["cost"], none)
+    assert np.array_equal(got, want)
+    if name == "situation1" and vm == 0:
+        with open(os.path.join(GOLDEN, "thesis_costs.json")) as f:
+            thesis = json.load(f)
+        ranked = sorted(int(c) for c in got if c != none)
+        assert ranked[:10] == thesis["lists"]["s1_with_banks"]
+        assert ranked[0] == 72206
+
+
+@pytest.mark.parametrize("n,nc,seed", [(2, 2048, 3), (6, 4096, 5), (16, 8192, 16), (22, 4096, 22)])
+def test_random_strikes_match_port_oracle(engine, port, n, nc, seed):
+    rng = np.random.RandomState(seed)
+    pos = _rand_layout(rng, n)
+    types = np.array([0] + [1] * (n - 1), dtype=np.int32)
+    ang = rng.uniform(0, 2 * np.pi, nc)
+    spd = rng.uniform(100, 5000, nc)
+    vx = (spd * np.cos(ang)).astype(np.float32)
+    vy = (spd * np.sin(ang)).astype(np.float32)
+    sc = rng.randint(1, 10**6, nc).astype(np.uint64)
+    bc = rng.randint(0, 10**6, nc).astype(np.uint64)
+    engine.set_states(pos, types, 1 << 1)
+    out = engine.evaluate(0, vx, vy, sc, bc, final_pos=True, event_log=True)
+    ora = port.evaluate(pos[None], types[None], 1 << 1, 0, vx, vy, sc, bc, threads=os.cpu_count() or 4, event_log=True)
+    c = compare_batch(out, ora)
+    print(f"N={n}: " + summary(c))
+    assert c["n_clean"] > 0.9 * nc
+    assert c["n_ok"] >= MIN_PARITY * c["n_clean"], summary(c)
+
+
+def test_random_strikes_match_reference_build(engine, ref):
+    """Same as above against the reference's own code (oracle/_ref/libref_oracle.so, prebuilt)."""
+    rng = np.random.RandomState(101)
+    n, nc = 16, 1024
+    pos = _rand_layout(rng, n)
+    types = np.array([0] + [1] * 9 + [2, 3, 4, 5, 6, 7], dtype=np.int32)
+    ang = rng.uniform(0, 2 * np.pi, nc)
+    spd = rng.uniform(100, 5000, nc)
+    vx = (spd * np.cos(ang)).astype(np.float32)
+    vy = (spd * np.sin(ang)).astype(np.float32)
+    mask = (1 << 1) | (1 << 7)
+    engine.set_states(pos, types, mask)
+    out = engine.evaluate(0, vx, vy, 100000, 5, final_pos=True, event_log=False)
+    ora = ref.evaluate(pos[None], types[None], mask, 0, vx, vy, 100000, 5, threads=os.cpu_count() or 4)
+    c = compare_batch(out, ora)
+    print(summary(c))
+    assert c["n_ok"] >= MIN_PARITY * c["n"] - 0.03 * c["n"]  # no tie information from the reference build
+
+
+def test_multi_state_absent_balls_and_empty_batch(engine, port):
+    """Ragged input: states with absent balls (type -1, as after pots), several states per launch, n = 0."""
+    rng = np.random.RandomState(9)
+    n, ns, per = 12, 5, 400
+    pos = np.stack([_rand_layout(rng, n) for _ in range(ns)])
+    types = np.tile(np.array([0] + [1] * (n - 1), dtype=np.int32), (ns, 1))
+    for s in range(ns):
+        types[s, rng.choice(np.arange(1, n), size=s, replace=False)] = -1
+    masks = np.array([2, 2, 6, 2, 2], dtype=np.uint32)
+    nc = ns * per
+    cs = np.repeat(np.arange(ns, dtype=np.int32), per)
+    ang = rng.uniform(0, 2 * np.pi, nc)
+    spd = rng.uniform(100, 5000, nc)
+    vx = (spd * np.cos(ang)).astype(np.float32)
+    vy = (spd * np.sin(ang)).astype(np.float32)
+    engine.set_states(pos, types, masks)
+    out = engine.evaluate(cs, vx, vy, 100000, 0, final_pos=True, event_log=True)
+    ora = port.evaluate(pos, types, masks, cs, vx, vy, 100000, 0, threads=4, event_log=True)
+    c = compare_batch(out, ora)
+    print(summary(c))
+    assert c["n_ok"] >= MIN_PARITY * c["n_clean"], summary(c)
+    empty = engine.evaluate(0, np.zeros(0, np.float32), np.zeros(0, np.float32), 1, 0)
+    assert len(empty["cost"]) == 0
+
+
+def test_grid_topk_gather_against_numpy_and_oracle(engine, port):
+    """Grid decode (K3), block top-k (K2) and gather: ids, ordering and ties exactly as numpy computes them
+    from the fetched per-candidate results; a sample of the grid against the oracle."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.random_layout(16, 16)
+    dirs, speeds = W.grid(256, 16)
+    ns = 3
+    spos = np.stack([pos, pos[::-1].copy(), pos])
+    stypes = np.stack([types, types[::-1].copy(), types])
+    base = np.array([0, 1000, 7], dtype=np.uint64)
+    engine.set_states(spos, stypes, 1 << 1, base)
+    total = engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    assert total == ns * 256 * 16
+    res = engine.fetch()
+    vx, vy = W.grid_velocities(dirs, speeds)
+    cs = np.repeat(np.arange(ns, dtype=np.int32), len(vx))
+    ora = port.evaluate(spos, stypes, 1 << 1, cs, np.tile(vx, ns), np.tile(vy, ns), W.GRID_SEARCH_COST, base[cs], threads=4)
+    c = compare_batch(res, ora)
+    print(summary(c))
+    assert c["n_ok"] >= MIN_PARITY * c["n_clean"], summary(c)
+    # top-k == stable sort of (cost, id) over valid candidates
+    valid = (res["flags"] & F_VALID) != 0
+    ids = np.nonzero(valid)[0]
+    order = np.lexsort((ids, res["cost"][ids]))
+    for k in (1, 7, 256, 1024):
+        tc, ti = engine.topk(k)
+        kk = min(k, len(ids))
+        assert np.array_equal(ti, ids[order][:kk].astype(np.uint64))
+        assert np.array_equal(tc, res["cost"][ids][order][:kk])
+    tc, ti = engine.topk(64)
+    gpos, gpot, gt = engine.gather(ti)
+    assert np.array_equal(gpos, res["final_pos"][ti.astype(np.int64)])
+    assert np.array_equal(gpot, res["potted"][ti.astype(np.int64)])
+    assert np.array_equal(gt, res["final_time"][ti.astype(np.int64)])
+    # a shard of the grid gives the same per-candidate results and global ids
+    lo, hi = W.shard_range(total, 1, 4)
+    engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=lo, count=hi - lo)
+    part = engine.fetch()
+    for key in ("cost", "flags", "potted", "n_events"):
+        assert np.array_equal(part[key], res[key][lo:hi])
+    tc2, ti2 = engine.topk(16)
+    sel = ids[(ids >= lo) & (ids < hi)]
+    o2 = np.lexsort((sel, res["cost"][sel]))
+    assert np.array_equal(ti2, sel[o2][:16].astype(np.uint64))
+
+
+def test_full_size_config2_properties(engine):
+    """BASELINE config 2 at full size (22-ball snooker layout, 1024 x 64 = 65 536 strikes): size-independent
+    properties -- determinism across launches, every candidate accounted for, flag consistency, sorted top-k."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.snooker22()
+    dirs, speeds = W.grid(1024, 64)
+    engine.set_states(pos, types, 1 << 1)
+    n = engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    assert n == 65536
+    a = engine.fetch()
+    engine.rerun()
+    b = engine.fetch()
+    for key in ("cost", "flags", "potted", "n_events", "final_time", "final_pos"):
+        assert np.array_equal(a[key], b[key]), key
+    fl = a["flags"]
+    done = (fl & F_COMPLETED) != 0
+    assert np.all(((fl & 4) != 0) | ((fl & 8) != 0) | done)           # every candidate ends in exactly one way
+    assert np.all(((fl & F_VALID) == 0) | done)                         # valid implies completed
+    assert np.all((a["cost"] == np.uint64(2**64 - 1)) == ~done)
+    assert np.all(a["n_events"][(fl & 4) != 0] == 30)                   # overflow = MAX_EVENTS reached
+    assert np.all(a["n_events"][done] >= 1)
+    assert np.all(a["cost"][done] <= W.GRID_SEARCH_COST)                # min(total, 1) * searchCost
+    tc, ti = engine.topk(1024)
+    assert np.all(np.diff(tc.astype(np.int64)) >= 0)
+    assert len(np.unique(ti)) == len(ti)
