@@ -3,6 +3,7 @@
 // the kernels of bcu_kernels.cu / bcu_topk.cu on one stream and copies results back.
 // There is no CPU path in this library.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <cmath>
 #include <cstdio>
@@ -75,10 +76,60 @@ struct bcu_engine {
     DevBuf<float> dGatherPos, dGatherTime;
     DevBuf<uint32_t> dGatherPotted;
 
+    // beam record blocks (bcu_merge.cu): local top-k, gathered from all ranks, merged
+    DevBuf<unsigned char> dBlockLocal, dBlockAll, dBlockMerged;
+    int beamK = 0;
+    bool haveBeam = false;
+    // user timer + measurement helpers
+    cudaEvent_t evT0 = nullptr, evT1 = nullptr;
+    DevBuf<unsigned char> dFlush;
+    DevBuf<double> dSink;
+    // NCCL (loaded lazily with dlopen; only needed for n_ranks > 1)
+    void* ncclLib = nullptr;
+    void* ncclComm = nullptr;
+    int nRanks = 1, rank = 0;
+    int64_t idBase = 0;  // global id of candidate 0 of the next bcu_evaluate (multi-GPU shards of explicit lists)
+
     LaunchParams last{};
     bool haveLast = false;
     int64_t lastFirst = 0;
 };
+
+// ---- NCCL through dlopen: the library has no link-time dependency on it -----------------------------------
+namespace {
+struct NcclApi {
+    struct Uid { char b[128]; };  // ncclUniqueId (NCCL_UNIQUE_ID_BYTES = 128), passed by value
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, Uid, int) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+bool load_nccl(const char* path, std::string* err) {
+    if (g_nccl.lib) return true;
+    const char* cands[] = {path, getenv("BCU_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    void* h = nullptr;
+    for (const char* c : cands) {
+        if (!c || !*c) continue;
+        h = dlopen(c, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) { *err = std::string("cannot dlopen NCCL: ") + dlerror(); return false; }
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+    g_nccl.AllGather = (decltype(g_nccl.AllGather))dlsym(h, "ncclAllGather");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.CommDestroy) {
+        *err = "NCCL library lacks required symbols";
+        return false;
+    }
+    g_nccl.lib = h;
+    return true;
+}
+}  // namespace
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -148,7 +199,8 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     e->rules.cueType = rules->cue_type;
     for (int i = 0; i < rules->n_types; ++i) e->rules.score[i] = rules->score[i];
     if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&e->evStart) != cudaSuccess || cudaEventCreate(&e->evStop) != cudaSuccess) {
+        cudaEventCreate(&e->evStart) != cudaSuccess || cudaEventCreate(&e->evStop) != cudaSuccess ||
+        cudaEventCreate(&e->evT0) != cudaSuccess || cudaEventCreate(&e->evT1) != cudaSuccess) {
         delete e;
         return BCU_ERR_CUDA;
     }
@@ -170,6 +222,10 @@ void bcu_destroy(bcu_engine* e) {
     e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release();
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
+    e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
+    if (e->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->ncclComm);
+    if (e->evT0) cudaEventDestroy(e->evT0);
+    if (e->evT1) cudaEventDestroy(e->evT1);
     if (e->evStart) cudaEventDestroy(e->evStart);
     if (e->evStop) cudaEventDestroy(e->evStop);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -291,7 +347,7 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
     rc = run(e, p, false);
     if (rc) return rc;
-    e->last = p; e->haveLast = true; e->lastFirst = 0;
+    e->last = p; e->haveLast = true; e->lastFirst = e->idBase;
     return copy_back(e, 0, n, out);
 }
 
@@ -410,6 +466,167 @@ int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* outPos, uin
         if (outTime) CK(cudaMemcpyAsync(outTime + i, e->dFinalTime.p + local, sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     }
     CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+// ---- one break level, device resident: evaluate -> top-k -> record block -> (allgather) -> merge -----------------
+static int topk_device(bcu_engine* e, int32_t k) {
+    const int64_t n = e->last.nCand;
+    const size_t sb = topk_scratch_bytes(n, k);
+    CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
+    CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
+                   e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
+    e->launches += 2;
+    return BCU_OK;
+}
+
+int bcu_level_select(bcu_engine* e, int32_t k) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast || !e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "bcu_level_select: no grid launch to select from");
+    if (k < 1 || k > 1024) return fail(e, BCU_ERR_INVALID, "bcu_level_select: k must be in 1..1024");
+    CK(cudaSetDevice(e->device));
+    int rc = topk_device(e, k);
+    if (rc) return rc;
+    const size_t bb = record_block_bytes(k, e->nBalls);
+    CK(e->dBlockLocal.reserve(bb)); CK(e->dBlockAll.reserve(bb * e->nRanks)); CK(e->dBlockMerged.reserve(bb));
+    CK(launch_pack_records(e->dTopCost.p, e->dTopId.p, k, e->lastFirst, e->dPotted.p, e->dFinalTime.p, e->dFinalPos.p,
+                           e->nBalls, e->dBlockLocal.p, e->stream));
+    e->launches += 1;
+    const void* gathered = e->dBlockLocal.p;
+    if (e->nRanks > 1) {
+        // the ONE collective of the path: per-GPU top-k records, ~ k * (24 + 8 N) bytes per rank
+        int nr = g_nccl.AllGather(e->dBlockLocal.p, e->dBlockAll.p, bb, /*ncclInt8*/ 0, e->ncclComm, e->stream);
+        if (nr != 0) {
+            e->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nr) : "error");
+            return BCU_ERR_CUDA;
+        }
+        gathered = e->dBlockAll.p;
+    }
+    CK(launch_merge_records(gathered, e->nRanks, k, e->nBalls, e->dBlockMerged.p, e->stream));
+    e->launches += 2;
+    e->beamK = k;
+    e->haveBeam = true;
+    return BCU_OK;  // asynchronous: bcu_fetch_beam / bcu_sync wait for it
+}
+
+int bcu_level_rerun(bcu_engine* e, int32_t k) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!e->haveLast) return fail(e, BCU_ERR_STATE, "bcu_level_rerun: nothing to re-run");
+    CK(cudaSetDevice(e->device));
+    int rc = run(e, e->last, false);
+    if (rc) return rc;
+    return bcu_level_select(e, k);
+}
+
+int bcu_fetch_beam(bcu_engine* e, int32_t* outCount, uint64_t* outCost, uint64_t* outId, uint32_t* outPotted,
+                   float* outTime, float* outPos) {
+    if (!e || !outCount) return BCU_ERR_INVALID;
+    if (!e->haveBeam) return fail(e, BCU_ERR_STATE, "bcu_fetch_beam: no bcu_level_select yet");
+    CK(cudaSetDevice(e->device));
+    const int k = e->beamK, NB = e->nBalls;
+    char* base = (char*)e->dBlockMerged.p;
+    std::vector<uint64_t> ids(k);
+    CK(cudaMemcpyAsync(ids.data(), base + (size_t)k * 8, (size_t)k * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (outCost) CK(cudaMemcpyAsync(outCost, base, (size_t)k * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (outPotted) CK(cudaMemcpyAsync(outPotted, base + (size_t)k * 16, (size_t)k * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (outTime) CK(cudaMemcpyAsync(outTime, base + (size_t)k * 20, (size_t)k * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (outPos) CK(cudaMemcpyAsync(outPos, base + (size_t)k * 24, (size_t)k * NB * 8, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    int cnt = 0;
+    while (cnt < k && ids[cnt] != ~0ull) cnt++;
+    if (outId) std::memcpy(outId, ids.data(), (size_t)k * 8);
+    *outCount = cnt;
+    return BCU_OK;
+}
+
+int bcu_set_id_base(bcu_engine* e, int64_t idBase) {
+    if (!e || idBase < 0) return BCU_ERR_INVALID;
+    e->idBase = idBase;
+    return BCU_OK;
+}
+
+int bcu_sync(bcu_engine* e) {
+    if (!e) return BCU_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+// ---- multi-GPU: one NCCL communicator per engine (one process per GPU) ------------------------------------------
+int bcu_comm_unique_id(const char* ncclLibPath, void* out128) {
+    std::string err;
+    if (!out128) return BCU_ERR_INVALID;
+    if (!load_nccl(ncclLibPath, &err)) return BCU_ERR_CUDA;
+    return g_nccl.GetUniqueId(out128) == 0 ? BCU_OK : BCU_ERR_CUDA;
+}
+
+int bcu_comm_init(bcu_engine* e, int32_t nRanks, int32_t rank, const void* uniqueId128, const char* ncclLibPath) {
+    if (!e) return BCU_ERR_INVALID;
+    if (nRanks < 1 || rank < 0 || rank >= nRanks) return fail(e, BCU_ERR_INVALID, "bcu_comm_init: bad rank / size");
+    if (nRanks == 1) { e->nRanks = 1; e->rank = 0; return BCU_OK; }
+    if (!uniqueId128) return fail(e, BCU_ERR_INVALID, "bcu_comm_init: unique id required");
+    if (!load_nccl(ncclLibPath, &e->err)) return BCU_ERR_CUDA;
+    CK(cudaSetDevice(e->device));
+    NcclApi::Uid uid;
+    std::memcpy(uid.b, uniqueId128, 128);
+    int nr = g_nccl.CommInitRank(&e->ncclComm, nRanks, uid, rank);
+    if (nr != 0) {
+        e->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nr) : "error");
+        return BCU_ERR_CUDA;
+    }
+    e->nRanks = nRanks;
+    e->rank = rank;
+    return BCU_OK;
+}
+
+// ---- measurement hooks --------------------------------------------------------------------------------------
+int bcu_timer_begin(bcu_engine* e) {
+    if (!e) return BCU_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventRecord(e->evT0, e->stream));
+    return BCU_OK;
+}
+
+int bcu_timer_end(bcu_engine* e, float* outMs) {
+    if (!e || !outMs) return BCU_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventRecord(e->evT1, e->stream));
+    CK(cudaEventSynchronize(e->evT1));
+    CK(cudaEventElapsedTime(outMs, e->evT0, e->evT1));
+    return BCU_OK;
+}
+
+int bcu_flush_l2(bcu_engine* e) {
+    if (!e) return BCU_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    const size_t bytes = (size_t)256 << 20;  // > 126 MB L2
+    CK(e->dFlush.reserve(bytes));
+    CK(launch_flush(e->dFlush.p, bytes, e->stream));
+    return BCU_OK;
+}
+
+int bcu_issue_rate(bcu_engine* e, int32_t kind, double* outGinstPerSec) {
+    if (!e || !outGinstPerSec || kind < 0 || kind > 3) return BCU_ERR_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(e->dSink.reserve(1));
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device));
+    const int ctas = sms * 8, iters = 1 << 15;
+    launch_issue_rate(kind, ctas, 1 << 10, e->dSink.p, e->stream);  // warm-up
+    float best = 1e30f;
+    int per = 0;
+    for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaEventRecord(e->evT0, e->stream));
+        per = launch_issue_rate(kind, ctas, iters, e->dSink.p, e->stream);
+        CK(cudaEventRecord(e->evT1, e->stream));
+        CK(cudaEventSynchronize(e->evT1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, e->evT0, e->evT1));
+        if (ms < best) best = ms;
+    }
+    CK(cudaGetLastError());
+    const double inst = (double)ctas * 256.0 * (double)iters * per;
+    *outGinstPerSec = inst / (best * 1e-3) / 1e9;
     return BCU_OK;
 }
 

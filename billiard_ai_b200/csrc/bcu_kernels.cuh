@@ -62,4 +62,14 @@ cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCa
                         cudaStream_t stream);
 size_t topk_scratch_bytes(int64_t nCand, int k);
 
+// beam records and their multi-GPU merge; see bcu_merge.cu
+size_t record_block_bytes(int k, int nBalls);
+cudaError_t launch_pack_records(const uint64_t* keyCost, const uint64_t* keyId, int k, int64_t firstCandidate,
+                                const uint32_t* potted, const float* finalTime, const float* finalPos, int nBalls,
+                                void* out, cudaStream_t stream);
+cudaError_t launch_merge_records(const void* gathered, int G, int k, int nBalls, void* out, cudaStream_t stream);
+// measurement helpers
+int launch_issue_rate(int kind, int ctas, int iters, double* sink, cudaStream_t stream);
+cudaError_t launch_flush(void* buf, size_t bytes, cudaStream_t stream);
+
 }  // namespace bcu

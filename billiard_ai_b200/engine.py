@@ -96,6 +96,7 @@ class Engine:
         self.n_balls = 0
         self.n_states = 0
         self._last_n = 0
+        self._beam_k = 0
 
     @classmethod
     def from_table(cls, tbl, scores, cue_type=0, device=0):
@@ -213,6 +214,62 @@ class Engine:
                                      _p(potted, C.c_uint32), _p(tm, C.c_float)), "bcu_gather")
         return pos, potted, tm
 
+    # ---- one break level, device resident ------------------------------------------------------------
+    def level_select(self, k):
+        self._ck(self.lib.bcu_level_select(self.h, C.c_int32(k)), "bcu_level_select")
+        self._beam_k = k
+
+    def level_rerun(self, k):
+        self._ck(self.lib.bcu_level_rerun(self.h, C.c_int32(k)), "bcu_level_rerun")
+        self._beam_k = k
+
+    def fetch_beam(self, with_pos=True):
+        k = self._beam_k
+        cost = np.zeros(k, np.uint64)
+        ids = np.zeros(k, np.uint64)
+        potted = np.zeros(k, np.uint32)
+        tm = np.zeros(k, np.float32)
+        pos = np.zeros((k, self.n_balls, 2), np.float32) if with_pos else None
+        cnt = C.c_int32(0)
+        self._ck(self.lib.bcu_fetch_beam(self.h, C.byref(cnt), _p(cost, C.c_uint64), _p(ids, C.c_uint64),
+                                         _p(potted, C.c_uint32), _p(tm, C.c_float),
+                                         _p(pos, C.c_float) if with_pos else _null(C.c_float)), "bcu_fetch_beam")
+        n = cnt.value
+        return dict(cost=cost[:n], id=ids[:n], potted=potted[:n], final_time=tm[:n],
+                    final_pos=pos[:n] if with_pos else None)
+
+    def set_id_base(self, base):
+        self._ck(self.lib.bcu_set_id_base(self.h, C.c_int64(base)), "bcu_set_id_base")
+
+    def sync(self):
+        self._ck(self.lib.bcu_sync(self.h), "bcu_sync")
+
+    # ---- multi-GPU -----------------------------------------------------------------------------------
+    @staticmethod
+    def nccl_library_path():
+        """torch's bundled NCCL (the same library torch.distributed uses in this process)."""
+        try:
+            import nvidia.nccl
+            d = os.path.join(os.path.dirname(nvidia.nccl.__path__[0] + "/"), "lib")
+            p = os.path.join(d, "libnccl.so.2")
+            if os.path.exists(p):
+                return p
+        except Exception:
+            pass
+        return "libnccl.so.2"
+
+    def comm_unique_id(self):
+        buf = (C.c_char * 128)()
+        rc = self.lib.bcu_comm_unique_id(self.nccl_library_path().encode(), buf)
+        if rc != 0:
+            raise BcuError("bcu_comm_unique_id failed (cannot load NCCL)")
+        return bytes(buf)
+
+    def comm_init(self, n_ranks, rank, unique_id=None):
+        uid = (C.c_char * 128).from_buffer_copy(unique_id) if unique_id is not None else None
+        self._ck(self.lib.bcu_comm_init(self.h, C.c_int32(n_ranks), C.c_int32(rank), uid,
+                                        self.nccl_library_path().encode()), "bcu_comm_init")
+
     # ---- single strike with layer trace -------------------------------------------------------------
     def simulate_trace(self, pos, types, vx, vy):
         pos = np.ascontiguousarray(pos, dtype=np.float32)
@@ -232,6 +289,22 @@ class Engine:
         ms = C.c_float(0)
         self._ck(self.lib.bcu_last_kernel_ms(self.h, C.byref(ms)), "bcu_last_kernel_ms")
         return ms.value
+
+    def timer_begin(self):
+        self._ck(self.lib.bcu_timer_begin(self.h), "bcu_timer_begin")
+
+    def timer_end(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.bcu_timer_end(self.h, C.byref(ms)), "bcu_timer_end")
+        return ms.value
+
+    def flush_l2(self):
+        self._ck(self.lib.bcu_flush_l2(self.h), "bcu_flush_l2")
+
+    def issue_rate(self, kind):
+        out = C.c_double(0)
+        self._ck(self.lib.bcu_issue_rate(self.h, C.c_int32(kind), C.byref(out)), "bcu_issue_rate")
+        return out.value
 
     def enable_counters(self, on=True):
         self._ck(self.lib.bcu_enable_counters(self.h, C.c_int(int(on))), "bcu_enable_counters")

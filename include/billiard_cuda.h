@@ -124,7 +124,36 @@ int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* out_pos, ui
 int bcu_simulate_trace(bcu_engine* e, int32_t n_balls, const float* pos, const int32_t* types, float vx, float vy,
                        int32_t* out_layers, float* out_times, float* out_rec);
 
+/* ---- one break level, device resident (billiard_search.cpp:224-244 expand + process.hpp:19-25 pop order) ----
+ * After bcu_evaluate_grid: select the k best VALID candidates by (cost, id), pack their end states into a record
+ * block, all-gather the blocks of all ranks (one ncclAllGather; skipped for a single rank) and merge them into
+ * the global top-k -- identical on every rank.  Asynchronous on the engine's stream. */
+int bcu_level_select(bcu_engine* e, int32_t k);
+/* Re-run the last grid launch and select again, everything resident (timing loops). */
+int bcu_level_rerun(bcu_engine* e, int32_t k);
+/* Merged beam, device -> host: *out_count valid entries (ascending); arrays sized for k (any may be NULL):
+ * out_pos [k][n_balls][2] = rest positions after the strike (potted balls keep their last position; see out_potted). */
+int bcu_fetch_beam(bcu_engine* e, int32_t* out_count, uint64_t* out_cost, uint64_t* out_id, uint32_t* out_potted,
+                   float* out_time, float* out_pos);
+int bcu_sync(bcu_engine* e);
+/* Global id of candidate 0 of subsequent bcu_evaluate calls (a rank's shard of an explicit candidate list);
+ * ids only matter as the tie-break of the top-k order. */
+int bcu_set_id_base(bcu_engine* e, int64_t id_base);
+
+/* ---- multi-GPU: one process per GPU, one NCCL communicator per engine -------------------------------------
+ * NCCL is dlopen'ed (nccl_lib_path, else $BCU_NCCL_LIB, else libnccl.so.2); rank 0 creates the 128-byte id and
+ * the caller distributes it (torch.distributed / MPI / a file). */
+int bcu_comm_unique_id(const char* nccl_lib_path, void* out128);
+int bcu_comm_init(bcu_engine* e, int32_t n_ranks, int32_t rank, const void* unique_id128, const char* nccl_lib_path);
+
 /* ---- measurement hooks -------------------------------------------------------------------------------- */
+/* CUDA-event timer on the engine's stream (the stream every kernel of this library is launched on) */
+int bcu_timer_begin(bcu_engine* e);
+int bcu_timer_end(bcu_engine* e, float* out_ms);
+/* writes a 256 MB buffer (> L2) on the engine's stream */
+int bcu_flush_l2(bcu_engine* e);
+/* vector-pipe issue rate in 1e9 thread-instructions/s: kind 0 DADD+DMUL, 1 DFMA, 2 FADD+FMUL, 3 FFMA */
+int bcu_issue_rate(bcu_engine* e, int32_t kind, double* out_ginst_per_s);
 /* ms of the last kernel launch (CUDA events on the engine's stream) */
 int bcu_last_kernel_ms(bcu_engine* e, float* out_ms);
 /* work counters of the last launch when enabled: {events, pair items, quartics, rail items, pocket items} */
