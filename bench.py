@@ -39,7 +39,7 @@ W_PAIR, W_RAIL, W_POCKET, W_ADVANCE, W_QUARTIC_FP64 = 25.0, 20.0, 20.0, 12.0, 10
 
 
 def workload_desc(world):
-    return {"workload": "config2: snooker 22-ball layout, 1-break search, 65536 strikes per GPU "
+    return {"workload": "config2: snooker 22-ball layout (open table, seed 22), 1-break search, 65536 strikes per GPU "
                         f"({N_DIRS}x{world} directions x {N_SPEEDS} speeds), beam {BEAM}",
             "n_balls": 22, "candidates_per_gpu": N_DIRS * N_SPEEDS, "candidates_total": N_DIRS * N_SPEEDS * world,
             "beam": BEAM, "l2": "flushed between timed steps (256 MB write, untimed)",
@@ -114,7 +114,7 @@ def reference_sample(world, n_sample):
 
 def time_reference(oracle, world, n_sample, threads):
     from billiard_ai_b200 import workloads as W
-    pos, types = W.snooker22()
+    pos, types = W.snooker22_open()
     vx, vy = reference_sample(world, n_sample)
     t0 = time.perf_counter()
     out = oracle.evaluate(pos[None], types[None], 1 << W.TYPE_CODE["RED"], 0, vx, vy, W.GRID_SEARCH_COST, 0,
@@ -172,7 +172,7 @@ def run_b200(args, rank, local_rank, world):
         dist.broadcast_object_list(box, src=0)
         eng.comm_init(world, rank, box[0])
 
-    pos, types = W.snooker22()
+    pos, types = W.snooker22_open()
     dirs, speeds = W.grid(N_DIRS * world, N_SPEEDS)
     total = len(dirs) * len(speeds)
     lo, hi = W.shard_range(total, rank, world)

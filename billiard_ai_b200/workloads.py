@@ -58,6 +58,17 @@ def random_layout(n, seed, radius=26.15, half_len=940.5, half_wid=471.5, min_gap
     return np.array(pos, dtype=np.float32), types
 
 
+def snooker22_open(seed=22):
+    """Config 2/4 layout used by bench.py: the 22 snooker balls (WHITE, 15 RED, 6 colours) at seeded random
+    non-overlapping positions (SURVEY.md 8d "seeded random non-overlapping (seed 22)") -- an open mid-frame table.
+    The racked layout of snooker22() has no valid RED pot within one strike (every candidate is invalid), which
+    makes it an edge case for the tests rather than a search workload."""
+    pos, _ = random_layout(22, seed)
+    types = np.array([TYPE_CODE["WHITE"]] + [TYPE_CODE["RED"]] * 15 +
+                     [TYPE_CODE[n] for n in ("YELLOW", "GREEN", "BROWN", "BLUE", "PINK", "BLACK")], dtype=np.int32)
+    return pos, types
+
+
 def random_tables(n_tables, n_balls, seed0=1000):
     """Config 5: table i seeded seed0 + i."""
     pos = np.zeros((n_tables, n_balls, 2), np.float32)

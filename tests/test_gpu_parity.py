@@ -239,7 +239,7 @@ def test_full_size_config2_properties(engine):
     """BASELINE config 2 at full size (22-ball snooker layout, 1024 x 64 = 65 536 strikes): size-independent
     properties -- determinism across launches, every candidate accounted for, flag consistency, sorted top-k."""
     from billiard_ai_b200 import workloads as W
-    pos, types = W.snooker22()
+    pos, types = W.snooker22_open()
     dirs, speeds = W.grid(1024, 64)
     engine.set_states(pos, types, 1 << 1)
     n = engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
@@ -258,5 +258,33 @@ def test_full_size_config2_properties(engine):
     assert np.all(a["n_events"][done] >= 1)
     assert np.all(a["cost"][done] <= W.GRID_SEARCH_COST)                # min(total, 1) * searchCost
     tc, ti = engine.topk(1024)
+    assert len(tc) == 1024
     assert np.all(np.diff(tc.astype(np.int64)) >= 0)
     assert len(np.unique(ti)) == len(ti)
+    # the device-resident level (top-k -> record block -> merge) returns the same beam
+    engine.level_select(1024)
+    beam = engine.fetch_beam()
+    assert np.array_equal(beam["cost"], tc) and np.array_equal(beam["id"], ti)
+    assert np.array_equal(beam["final_pos"], a["final_pos"][ti.astype(np.int64)])
+    assert np.array_equal(beam["potted"], a["potted"][ti.astype(np.int64)])
+
+
+def test_racked_layout_has_no_valid_strike_and_gives_an_empty_beam(engine, port):
+    """Edge case: on the racked 22-ball layout no single strike pots a RED cleanly, so every candidate is invalid,
+    the top-k is empty and the beam has zero entries (the reference's search would return no solution)."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.snooker22()
+    dirs, speeds = W.grid(128, 16)
+    engine.set_states(pos, types, 1 << 1)
+    engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    res = engine.fetch()
+    vx, vy = W.grid_velocities(dirs, speeds)
+    ora = port.evaluate(pos[None], types[None], 1 << 1, 0, vx, vy, W.GRID_SEARCH_COST, 0, threads=4)
+    c = compare_batch(res, ora)
+    print(summary(c))
+    assert c["n_ok"] >= MIN_PARITY * c["n_clean"], summary(c)
+    assert not np.any(res["flags"] & F_VALID)
+    tc, ti = engine.topk(64)
+    assert len(tc) == 0
+    engine.level_select(64)
+    assert len(engine.fetch_beam()["cost"]) == 0
