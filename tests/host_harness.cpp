@@ -3,6 +3,7 @@
 // CPU-only test tier.  This object is never loaded by the product (which has no CPU path); it lives in
 // tests/_build/.
 #include <cstdint>
+#define BCU_COUNT_FALLBACKS 1
 #include "../billiard_ai_b200/csrc/bcu_physics.cuh"
 
 using namespace bcu;
@@ -47,12 +48,29 @@ int hh_time_to_collision_batch(int64_t n, const float* p1, const float* v1, cons
     return 0;
 }
 
+long long hh_fallback_count(int reset) { long long v = g_fallbacks; if (reset) g_fallbacks = 0; return v; }
+
 // complex helpers, for direct checks against glibc / libgcc
 void hh_csqrt(double re, double im, double* out2) { cplx r = g_csqrt(c_make(re, im)); out2[0] = r.re; out2[1] = r.im; }
 void hh_clog(double re, double im, double* out2) { cplx r = g_clog(c_make(re, im)); out2[0] = r.re; out2[1] = r.im; }
 void hh_cdiv(double a, double b, double c, double d, double* out2) { cplx r = c_div(c_make(a, b), c_make(c, d)); out2[0] = r.re; out2[1] = r.im; }
 double hh_hypot(double x, double y) { return g_hypot(x, y); }
 void hh_cpow(double re, double im, double y, double* out2) { cplx r = c_pow_real(c_make(re, im), y); out2[0] = r.re; out2[1] = r.im; }
+
+// glibc itself, called from C so that nothing (numpy SIMD loops, ...) stands between the test and libm
+void hh_glibc_batch(int which, int64_t n, const double* x, const double* y, double* out, double* out2) {
+    for (int64_t i = 0; i < n; ++i) {
+        switch (which) {
+            case 0: out[i] = ::exp(x[i]); break;
+            case 1: out[i] = ::log(x[i]); break;
+            case 2: out[i] = ::log1p(x[i]); break;
+            case 3: out[i] = ::pow(x[i], y[i]); break;
+            case 4: out[i] = ::atan2(y[i], x[i]); break;
+            case 5: ::sincos(x[i], &out[i], &out2[i]); break;
+            case 6: out[i] = ::hypot(x[i], y[i]); break;
+        }
+    }
+}
 
 double hh_exp(double x) { return g_exp(x); }
 double hh_log(double x) { return g_log(x); }
