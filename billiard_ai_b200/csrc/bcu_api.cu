@@ -67,7 +67,7 @@ struct bcu_engine {
     DevBuf<float> dFinalTime, dFinalPos;
     DevBuf<int4> dEventLog;
     DevBuf<float> dTraceTimes, dTraceRec;
-    DevBuf<unsigned long long> dCounters;
+    DevBuf<unsigned long long> dCounters, dNextCand;
     // top-k
     DevBuf<unsigned char> dTopkScratch;
     DevBuf<uint64_t> dTopCost, dTopId;
@@ -219,7 +219,7 @@ void bcu_destroy(bcu_engine* e) {
     e->dCandState.release(); e->dVx.release(); e->dVy.release(); e->dSearchCost.release(); e->dBaseCost.release();
     e->dDirs.release(); e->dSpeeds.release();
     e->dCost.release(); e->dFlags.release(); e->dPotted.release(); e->dFinalTime.release(); e->dFinalPos.release();
-    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release();
+    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dNextCand.release();
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
@@ -295,7 +295,8 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
     if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
     if (p.out.eventLog) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
     CK(cudaEventRecord(e->evStart, e->stream));
-    CK(launch_simulate(p, trace, e->maxCtas, e->stream));
+    CK(e->dNextCand.reserve(1));
+    CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
     CK(cudaEventRecord(e->evStop, e->stream));
     e->launches++;
     return BCU_OK;

@@ -53,7 +53,7 @@ struct LaunchParams {
 };
 
 void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
-cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, cudaStream_t stream);
+cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, unsigned long long* nextCand, cudaStream_t stream);
 int simulate_max_ctas(int device);
 
 // top-k selection on (cost, candidate id) among VALID candidates; see bcu_topk.cu
