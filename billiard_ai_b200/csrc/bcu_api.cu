@@ -169,7 +169,7 @@ const char* bcu_version(void) { return "billiard_cuda 0.1 (sm_100a)"; }
 int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int device, bcu_engine** out) {
     if (!out) return BCU_ERR_INVALID;
     *out = nullptr;
-    if (!table || !rules || !table->rails || !table->pockets || !rules->score) return BCU_ERR_INVALID;
+    if (!table || !rules || (!table->rails && !table->rails_derived) || !table->pockets || !rules->score) return BCU_ERR_INVALID;
     if (table->n_rails < 0 || table->n_rails > MAX_RAILS || table->n_pockets < 0 || table->n_pockets > MAX_POCKETS ||
         rules->n_types < 1 || rules->n_types > MAX_TYPES)
         return BCU_ERR_INVALID;
@@ -188,8 +188,17 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     e->table.diameter = table->ball_radius * 2;  // util.cpp:65: conf._ball._diameter = ballRadius * 2
     e->table.diameterSq = e->table.diameter * e->table.diameter;
     e->railDerived.resize((size_t)table->n_rails * 6);
-    for (int i = 0; i < table->n_rails; ++i)
-        derive_rail(table->rails + 6 * i, table->ball_radius, &e->table.rails[i], &e->railDerived[6 * i]);
+    for (int i = 0; i < table->n_rails; ++i) {
+        if (table->rails_derived) {
+            const float* d = table->rails_derived + 6 * i;
+            RailGeom& g = e->table.rails[i];
+            g.nx = d[0]; g.ny = d[1]; g.sx = d[2]; g.sy = d[3];
+            g.dx = d[4] - d[2]; g.dy = d[5] - d[3];  // billiard_physics.cpp:731-734
+            std::memcpy(&e->railDerived[6 * i], d, 6 * sizeof(float));
+        } else {
+            derive_rail(table->rails + 6 * i, table->ball_radius, &e->table.rails[i], &e->railDerived[6 * i]);
+        }
+    }
     for (int i = 0; i < table->n_pockets; ++i) {
         const float* p = table->pockets + 3 * i;
         e->table.pockets[i].x = p[0]; e->table.pockets[i].y = p[1]; e->table.pockets[i].r = p[2];

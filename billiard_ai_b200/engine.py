@@ -30,7 +30,8 @@ class BcuError(RuntimeError):
 
 class _TableDesc(C.Structure):
     _fields_ = [("n_rails", C.c_int32), ("n_pockets", C.c_int32), ("ball_radius", C.c_float),
-                ("rails", C.POINTER(C.c_float)), ("pockets", C.POINTER(C.c_float))]
+                ("rails", C.POINTER(C.c_float)), ("pockets", C.POINTER(C.c_float)),
+                ("rails_derived", C.POINTER(C.c_float))]
 
 
 class _RulesDesc(C.Structure):
@@ -85,7 +86,7 @@ class Engine:
         self._pockets = np.ascontiguousarray(np.asarray(pockets3, dtype=np.float32)[:, :3])
         self._scores = np.ascontiguousarray(scores, dtype=np.float64)
         td = _TableDesc(len(self._rails), len(self._pockets), C.c_float(np.float32(ball_radius)),
-                        _p(self._rails, C.c_float), _p(self._pockets, C.c_float))
+                        _p(self._rails, C.c_float), _p(self._pockets, C.c_float), _null(C.c_float))
         rd = _RulesDesc(len(self._scores), int(cue_type), _p(self._scores, C.c_double))
         h = C.c_void_p()
         rc = self.lib.bcu_create(C.byref(td), C.byref(rd), C.c_int(device), C.byref(h))

@@ -58,6 +58,10 @@ typedef struct {
     float ball_radius;
     const float* rails;
     const float* pockets;
+    /* Optional (may be NULL): n_rails x {normal.xy, shiftedStart.xy, shiftedEnd.xy} = Rail::_normal, _shiftedStart,
+     * _shiftedEnd as the reference's Rail objects already hold them (type.hpp:75-77).  When given it is used
+     * instead of deriving the geometry from `rails` (which may then be NULL). */
+    const float* rails_derived;
 } bcu_table_desc;
 
 /* Rules as data (the reference's std::function rules, type.hpp:324-332, cannot run on a device):

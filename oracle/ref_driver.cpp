@@ -210,6 +210,10 @@ int ref_set_rules(const char* typeNames, const double* scores) {
     return 0;
 }
 
+// The Configuration built by ref_set_table / ref_set_rules, for test programs compiled against the reference's
+// headers (tests/host_mirror_check.cpp).
+const void* ref_get_configuration(void) { return &g.conf; }
+
 void ref_set_toggles(int depthSearchEnabled, int velocityMultiplyEnabled) {
     g.conf._depthSearchEnabled = depthSearchEnabled != 0;
     g.conf._velocityMultiplyEnabled = velocityMultiplyEnabled != 0;

@@ -288,3 +288,37 @@ def test_racked_layout_has_no_valid_strike_and_gives_an_empty_beam(engine, port)
     assert len(tc) == 0
     engine.level_select(64)
     assert len(engine.fetch_beam()["cost"]) == 0
+
+
+def test_cpp_host_mirror_returns_the_reference_system(ref):
+    """billiard_ai_b200/host/billiard_cuda_search.hpp, compiled against the reference's own headers
+    (oracle/_ref/libmirror_check.so): Engine::simulate(state, velocity) must return the same node::System as
+    billiard::search::simulate(state, velocity, config) -- every node, BallState bit, cause id and the
+    _nextRolling / _lastRailCollisions bookkeeping -- and nullopt for the same strikes."""
+    import ctypes as C
+    from oracle_lib import ORACLE_DIR, TYPE_NAMES
+    so = os.path.join(ORACLE_DIR, "_ref", "libmirror_check.so")
+    if not os.path.exists(so):
+        pytest.skip("libmirror_check.so not built (needs /root/reference at build time)")
+    lib = C.CDLL(so)
+    rng = np.random.RandomState(77)
+    total_compared = 0
+    for n in (3, 9, 16):
+        pos = _rand_layout(rng, n)
+        types = np.array([0] + [1] * (n - 1), dtype=np.int32)
+        types[-1] = 7
+        ns = 150
+        ang = rng.uniform(0, 2 * np.pi, ns)
+        spd = rng.uniform(300, 5000, ns)
+        vx = (spd * np.cos(ang)).astype(np.float32)
+        vy = (spd * np.sin(ang)).astype(np.float32)
+        names = (C.c_char_p * len(TYPE_NAMES))(*[t.encode() for t in TYPE_NAMES])
+        compared, nullopt = C.c_int(0), C.c_int(0)
+        bad = lib.mirror_check(C.c_int(n), pos.ctypes.data_as(C.POINTER(C.c_float)), names, C.c_int(len(TYPE_NAMES)),
+                               types.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int(ns),
+                               vx.ctypes.data_as(C.POINTER(C.c_float)), vy.ctypes.data_as(C.POINTER(C.c_float)),
+                               C.byref(compared), C.byref(nullopt))
+        print(f"N={n}: {compared.value} systems compared, {nullopt.value} nullopt on both sides, {bad} differ")
+        assert bad == 0
+        total_compared += compared.value
+    assert total_compared > 350
