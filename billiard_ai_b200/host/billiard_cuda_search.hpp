@@ -104,11 +104,23 @@ public:
         if (layers == 0) return std::nullopt;  // billiard_search.cpp:170-174
         const float al = physics::accelerationLength(), sl = physics::slideAccelerationLength();
         node::System system;
+        std::unordered_map<std::string, node::Node> previous;
         for (int l = 0; l < layers; ++l) {
             std::unordered_map<std::string, node::Node> nodes;
             for (int b = 0; b < n; ++b) {
                 const float* r = &rec[((size_t)l * n + b) * BCU_TRACE_REC];
                 const Ball& ball = state._balls[b];
+                if (r[0] < 0.0f) continue;  // no such ball
+                {
+                    // createLayer copies the nodes of static balls (at rest / potted) unchanged (billiard_search.cpp:1965-1966)
+                    const auto staticType = (node::NodeType)(int)r[0];
+                    auto it = previous.find(ball._id);
+                    if (it != previous.end() && it->second._type == staticType &&
+                        (staticType == node::BALL_POTTING || staticType == node::BALL_IN_REST)) {
+                        nodes.insert(*it);
+                        continue;
+                    }
+                }
                 const bool afterRolling = r[5] != 0.0f;
                 const bool beforeRolling = l > 0 ? rec[((size_t)(l - 1) * n + b) * BCU_TRACE_REC + 5] != 0.0f : false;
                 const state::BallState after{glm::vec2{r[1], r[2]}, glm::vec2{r[3], r[4]}, al, sl, afterRolling};
@@ -140,6 +152,7 @@ public:
                 }
             }
             system.append(node::Layer{times[l], nodes});  // the reference's own bookkeeping (type.cpp:467-531)
+            previous = std::move(nodes);
         }
         return system;
     }
