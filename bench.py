@@ -151,7 +151,7 @@ def run_reference(args, rank, world):
             "config": workload_desc(world), "events_per_sec": tot_ev / tot_t,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- B200 arm -------------------------------------------------------------------------------------------------
@@ -315,12 +315,24 @@ def run_b200(args, rank, local_rank, world):
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
             "best_strike": {"cost": int(beam["cost"][0]), "id": int(beam["id"][0])} if len(beam["cost"]) else None}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else (NCCL banners, library chatter) was sent to stderr."""
+    REAL_STDOUT.write(json.dumps(line) + "\n")
+    REAL_STDOUT.flush()
+
+
+REAL_STDOUT = sys.stdout
+
+
 def main():
+    global REAL_STDOUT
+    REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)  # native libraries that print to fd 1 (e.g. "NCCL version ...") must not pollute the result line
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
