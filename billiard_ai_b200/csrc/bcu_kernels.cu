@@ -568,14 +568,14 @@ __global__ void __launch_bounds__(V2_WARPS * 32) simulate_candidates_v2(LaunchPa
             __syncwarp();
         }
     };
-    #pragma unroll
+    #pragma unroll 1
     for (int s = 0; s < S; ++s) refill(ws.slot[s]);
 
     for (;;) {
         // ---- A: per-slot masks, global dynamic-ball list, per-ball items (rest, rolling) --------------------------
         int Dtot = 0;
         bool anyActive = false;
-        #pragma unroll
+        #pragma unroll 1
         for (int s = 0; s < S; ++s) {
             SlotState& sl = ws.slot[s];
             if (sl.cand < 0) continue;
@@ -711,8 +711,12 @@ __global__ void __launch_bounds__(V2_WARPS * 32) simulate_candidates_v2(LaunchPa
                     if (o != b && (oStatic || (oDyn && b < o))) {
                         const float4 s1 = sl.pv[b], s2 = sl.pv[o];
                         const v2 p1 = mk(s1.x, s1.y), v1 = mk(s1.z, s1.w), p2 = mk(s2.x, s2.y), w2 = mk(s2.z, s2.w);
-                        bool pass = collision_precheck(v1, p1, w2, p2, diameter);
-                        if (!pass && oDyn) pass = collision_precheck(w2, p2, v1, p1, diameter);  // o's own turn
+                        // the reference tests b -> o and, for a dynamic partner, o -> b on o's own turn; the quantised
+                        // coefficients of both orders are identical, so one job covers both
+                        bool pass = false;
+                        #pragma unroll 1
+                        for (int turn = 0; turn < (oDyn ? 2 : 1) && !pass; ++turn)
+                            pass = turn == 0 ? collision_precheck(v1, p1, w2, p2, diameter) : collision_precheck(w2, p2, v1, p1, diameter);
                         if (pass) {
                             const float4 a1 = sl.na[b], a2 = sl.na[o];
                             collision_coefficients(mk(a1.z, a1.w), v1, p1, mk(a2.z, a2.w), w2, p2, diameter, co);
@@ -750,7 +754,7 @@ __global__ void __launch_bounds__(V2_WARPS * 32) simulate_candidates_v2(LaunchPa
         __syncwarp();
 
         // ---- C: apply the winning event of every slot (createLayer :1957-1992, System::append type.cpp:467-531) ------
-        #pragma unroll
+        #pragma unroll 1
         for (int s = 0; s < S; ++s) {
             SlotState& sl = ws.slot[s];
             if (sl.cand < 0) continue;
@@ -809,10 +813,12 @@ __global__ void __launch_bounds__(V2_WARPS * 32) simulate_candidates_v2(LaunchPa
                             const bool oroll = sl.rolling[other] != 0;
                             const v2 opos = advance_position(mk(oa4.z, oa4.w), mk(os.z, os.w), dt, mk(os.x, os.y));
                             const v2 ovel = advance_velocity(mk(oa4.z, oa4.w), mk(os.z, os.w), dt);
-                            v2 o1, o2;
-                            if (lane == evBall) elastic_collision(npos, nvel, opos, ovel, rolling, oroll, pc, &o1, &o2);
-                            else elastic_collision(opos, ovel, npos, nvel, oroll, rolling, pc, &o2, &o1);
-                            pos = npos; vel = o1; kind = K_COLLISION; cause = other;
+                            // ball1 = evBall, ball2 = evPartner: one call site, operands swapped by select
+                            const bool first = lane == evBall;
+                            v2 oa, ob;
+                            elastic_collision(first ? npos : opos, first ? nvel : ovel, first ? opos : npos, first ? ovel : nvel,
+                                              first ? rolling : oroll, first ? oroll : rolling, pc, &oa, &ob);
+                            pos = npos; vel = first ? oa : ob; kind = K_COLLISION; cause = other;
                         }
                         changed = true;
                     }

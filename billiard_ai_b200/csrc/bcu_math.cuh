@@ -44,7 +44,7 @@ BCU_HD bool c_eq0(cplx a) { return a.re == 0.0 && a.im == 0.0; }
 // libgcc2.c __divdc3 (GCC 13): Smith's algorithm with Baudin-Smith scaling.  Scalings are by
 // powers of two and only trigger for |denominator| outside [2^-52 .. DBL_MAX/2], or numerators
 // below DBL_MIN; kept for fidelity.
-BCU_HD cplx c_div(cplx n, cplx dd) {
+BCU_HD_NOINLINE cplx c_div(cplx n, cplx dd) {
     double a = n.re, b = n.im, c = dd.re, d = dd.im;
     const double RBIG = 1.7976931348623157e308 / 2;
     const double RMIN = 2.2250738585072014e-308;
@@ -125,7 +125,7 @@ BCU_HD double g_hypot(double x, double y) {
 }
 
 // glibc math/s_csqrt_template.c, finite operands (the quartic never feeds inf; NaN propagates).
-BCU_HD cplx g_csqrt(cplx x) {
+BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
     const double DMIN = 2.2250738585072014e-308, DMAX = 1.7976931348623157e308;
     cplx res;
     if (x.im == 0.0) {
@@ -250,7 +250,7 @@ BCU_HD cplx g_clog(cplx x) {
 }
 
 // libstdc++ <complex> std::pow(const complex<double>&, const double&) with _GLIBCXX_USE_C99_COMPLEX.
-BCU_HD cplx c_pow_real(cplx x, double y) {
+BCU_HD_NOINLINE cplx c_pow_real(cplx x, double y) {
     if (x.im == 0.0 && x.re > 0.0) return c_make(g_pow(x.re, y), 0.0);
     cplx t = g_clog(x);
     double rho = g_exp(y * t.re);
