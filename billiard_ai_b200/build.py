@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libbilliard_cuda.so")
-SOURCES = ["bcu_kernels.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu"]
+SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
@@ -25,22 +25,44 @@ def nvcc_path():
     return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 
 
+OBJDIR = os.path.join(HERE, "_build")
+
+
+def _deps():
+    return [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "billiard_cuda.h")]
+
+
 def needs_build():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "billiard_cuda.h")]
-    return any(os.path.getmtime(d) > t for d in deps)
+    return any(os.path.getmtime(d) > t for d in _deps())
 
 
 def build(force=False, verbose=False, extra=()):
+    """One object per translation unit (compiled in parallel, rebuilt only when a dependency is newer), then one link."""
     if not force and not needs_build():
         return OUT
-    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT]
-    if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-        print(" ".join(cmd))
-    subprocess.check_call(cmd)
+    os.makedirs(OBJDIR, exist_ok=True)
+    newest = max(os.path.getmtime(d) for d in _deps() if not d.endswith(".cu"))
+    flags = [f for f in NVCC_FLAGS if f not in ("-shared", "-ldl")]
+    procs = []
+    objs = []
+    for src in SOURCES:
+        obj = os.path.join(OBJDIR, src.replace(".cu", ".o"))
+        objs.append(obj)
+        spath = os.path.join(CSRC, src)
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(newest, os.path.getmtime(spath)):
+            continue
+        cmd = [nvcc_path()] + flags + list(extra) + ["-c", spath, "-o", obj]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+            print(" ".join(cmd))
+        procs.append((cmd, subprocess.Popen(cmd)))
+    for cmd, pr in procs:
+        if pr.wait() != 0:
+            raise subprocess.CalledProcessError(pr.returncode, cmd)
+    subprocess.check_call([nvcc_path(), "-shared", "-o", OUT] + objs + ["-ldl"])
     return OUT
 
 

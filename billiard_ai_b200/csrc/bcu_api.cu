@@ -68,6 +68,9 @@ struct bcu_engine {
     DevBuf<int4> dEventLog;
     DevBuf<float> dTraceTimes, dTraceRec;
     DevBuf<unsigned long long> dCounters, dNextCand;
+    DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
+    int sms = 148;
+    int kernelVersion = 3;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
     // top-k
     DevBuf<unsigned char> dTopkScratch;
     DevBuf<uint64_t> dTopCost, dTopId;
@@ -215,6 +218,8 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     }
     upload_constants(e->table, e->rules, e->stream);
     e->maxCtas = simulate_max_ctas(device);
+    cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
+    if (const char* kv = getenv("BCU_KERNEL")) e->kernelVersion = atoi(kv) == 2 ? 2 : 3;
     if (cudaGetLastError() != cudaSuccess) { delete e; return BCU_ERR_CUDA; }
     *out = e;
     return BCU_OK;
@@ -228,7 +233,7 @@ void bcu_destroy(bcu_engine* e) {
     e->dCandState.release(); e->dVx.release(); e->dVy.release(); e->dSearchCost.release(); e->dBaseCost.release();
     e->dDirs.release(); e->dSpeeds.release();
     e->dCost.release(); e->dFlags.release(); e->dPotted.release(); e->dFinalTime.release(); e->dFinalPos.release();
-    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dNextCand.release();
+    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dNextCand.release(); e->dPipeWs.release();
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
@@ -304,10 +309,33 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
     if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
     if (p.out.eventLog) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
     CK(cudaEventRecord(e->evStart, e->stream));
-    CK(e->dNextCand.reserve(1));
-    CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
+    if (trace || e->kernelVersion == 2) {
+        CK(e->dNextCand.reserve(1));
+        CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
+        e->launches++;
+    } else {
+        // batch path: chunks of at most PIPE_MAX_STRIKES strikes through the event-synchronous pipeline
+        const int64_t chunk = p.nCand < PIPE_MAX_STRIKES ? p.nCand : PIPE_MAX_STRIKES;
+        PipeWorkspace ws{};
+        CK(e->dPipeWs.reserve(pipeline_workspace_bytes(chunk, p.states.nBalls, nullptr)));
+        ws.base = e->dPipeWs.p;
+        pipeline_workspace_bytes(chunk, p.states.nBalls, &ws);
+        for (int64_t off = 0; off < p.nCand; off += chunk) {
+            LaunchParams q = p;
+            q.nCand = p.nCand - off < chunk ? p.nCand - off : chunk;
+            if (q.src.gridDirs > 0) {
+                q.src.firstCandidate += off;
+            } else {
+                q.src.stateIdx += off; q.src.vx += off; q.src.vy += off; q.src.searchCost += off; q.src.baseCost += off;
+            }
+            q.out.cost += off; q.out.flags += off; q.out.potted += off; q.out.finalTime += off;
+            if (q.out.finalPos) q.out.finalPos += (size_t)off * p.states.nBalls * 2;
+            if (q.out.eventLog) q.out.eventLog += (size_t)off * 32;
+            CK(launch_pipeline(q, ws, e->sms, e->stream));
+            e->launches += pipeline_launch_count();
+        }
+    }
     CK(cudaEventRecord(e->evStop, e->stream));
-    e->launches++;
     return BCU_OK;
 }
 

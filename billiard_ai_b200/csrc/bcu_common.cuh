@@ -13,7 +13,7 @@
 #define BCU_D __device__ __forceinline__
 // large routines called from several places of the quartic: one out-of-line copy each keeps the kernel's instruction
 // footprint inside the instruction cache (ncu on the fully inlined build: "no_instruction" was the top stall)
-#define BCU_HD_NOINLINE __host__ __device__ __noinline__
+#define BCU_HD_NOINLINE inline __host__ __device__ __noinline__
 #else
 #define BCU_HD inline
 #define BCU_D inline

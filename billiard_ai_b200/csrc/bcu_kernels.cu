@@ -885,6 +885,7 @@ void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream
     cudaMemcpyToSymbolAsync(c_table, &table, sizeof(TableGeom), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(c_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(c_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
+    pipeline_upload_constants(table, rules, stream);
     cudaStreamSynchronize(stream);
 }
 

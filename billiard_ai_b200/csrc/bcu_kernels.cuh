@@ -52,6 +52,36 @@ struct LaunchParams {
     Results out;
 };
 
+// ---- K1 v3, the event-synchronous batch pipeline (bcu_pipeline.cu) ----------------------------------------------
+constexpr int64_t PIPE_MAX_STRIKES = 1 << 20;   // per launch; larger batches are chunked by the caller
+constexpr int PIPE_JOBS_PER_STRIKE = 16;         // quartic-queue capacity per strike and round (overflow is solved in place)
+struct PipeWorkspace {
+    void* base;
+    int64_t n;                 // strikes this layout was made for
+    size_t dynCap, jobCap;
+    // per ball [n][nBalls]
+    float4* pv;                // pos.xy, vel.xy
+    float4* na;                // velNormed.xy, acc.xy   (state::BallState, type.cpp:176-184)
+    float* nextRolling;        // < 0: none  (System::_nextRolling, type.cpp:478-527)
+    uint32_t* meta;            // kind | rolling << 8 | (lastRail + 1) << 16 | (type + 1) << 24
+    // per strike
+    unsigned long long* key;   // [3][n] (ordered time bits << 32 | evaluation-order code), by round % 3
+    float* T;                  // [2][n] layer time, by round & 1
+    uint32_t* dynMask;         // [n]
+    uint32_t* restMask;        // [n]
+    // stream-compacted lists, by round & 1
+    uint32_t* live;            // [2][n] strike ids
+    uint32_t* dyn;             // [2][dynCap] strike << 5 | ball
+    uint32_t* counts;          // [rounds + 1][4] {live, dynamic balls, quartic jobs, -}
+    // quartic jobs of the round
+    float* jobCo;              // [5][jobCap]
+    uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner << 1 | partner is dynamic
+};
+size_t pipeline_workspace_bytes(int64_t n, int nBalls, PipeWorkspace* layout);
+void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
+cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& w, int sms, cudaStream_t stream);
+int pipeline_launch_count();
+
 void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
 cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, unsigned long long* nextCand, cudaStream_t stream);
 int simulate_max_ctas(int device);

@@ -1,0 +1,698 @@
+// K1 v3: the event-synchronous strike pipeline (the batch path of bcu_evaluate / bcu_evaluate_grid).
+//
+// Same arithmetic as simulate_candidates (bcu_kernels.cu, kept for the single-strike trace), but decomposed so that
+// every kernel is small (fits the instruction caches), dense (one thread per *item*, not per ball) and can be tuned
+// on its own.  ncu on the warp-per-strike kernels showed what bounds this path: 13-15 of 32 lanes active and an
+// instruction-fetch stall (`no_instruction`) of 24 cycles per issue from a 160 KB instruction footprint.
+//
+// All strikes of a launch advance one event per ROUND (the reference's event loop, billiard_search.cpp:1370-1381,
+// turned inside out).  State lives in HBM/L2 as structure-of-arrays; per round three kernels run on the stream:
+//
+//   items_kernel    one thread per (dynamic ball x rail | pocket | partner ball) item of every live strike
+//                   (nextRailCollision :1639-1682, nextPocketCollision :1684-1714, nextBallCollision :1603-1637).
+//                   A cheap first stage filters; survivors are compacted per CTA in shared memory so the second
+//                   stages (rail / pocket quadratics, quantised quartic coefficients) run on dense threads.
+//                   Rail / pocket times go to the strike's 64-bit (time, evaluation order) key with atomicMin -- the
+//                   reference's strict-'<' first-evaluated-wins choice (:2002-2013); ball pairs become quartic jobs
+//                   in a global queue.
+//   quartic_kernel  one thread per job: the FP64 complex closed-form quartic (billiard_physics.cpp:470-560).
+//   apply_kernel    one thread per live strike applies the winning event (createLayer :1957-1992, System::append
+//                   type.cpp:467-531), finishes strikes that reached their final layer (rules + simulationCost
+//                   :1388-1405, :1473-1532) and one thread per other dynamic ball advances it in closed form; both
+//                   offer the rest / rolling times of the next round (nextBallInRest :1590, nextRolling :1575) and
+//                   build the next round's stream-compacted lists of live strikes and dynamic balls.
+//
+// Keys are triple-buffered by round (read r%3, offered (r+1)%3, reset (r+2)%3) and layer times double-buffered, so no
+// kernel reads a word another thread of the same launch writes.
+#include <cuda_runtime.h>
+
+#include "bcu_kernels.cuh"
+#include "bcu_physics.cuh"
+
+namespace bcu {
+
+namespace {
+
+__constant__ TableGeom p_table;
+__constant__ RulesData p_rules;
+__constant__ PhysConst p_phys;
+
+constexpr int ROUNDS = MAX_EVENTS + 1;  // round r applies event r+1; round MAX_EVENTS only flags overflow
+constexpr int ITEM_BLOCK = 256;
+constexpr int ITEM_IPT = 4;            // stage-1 items per thread per tile
+constexpr int QUARTIC_BLOCK = 128;
+constexpr int APPLY_BLOCK = 256;
+
+enum Category : uint32_t { CAT_REST = 0, CAT_ROLLING = 1, CAT_STATIC_PAIR = 2, CAT_DYNAMIC_PAIR = 3, CAT_RAIL = 4, CAT_POCKET = 5 };
+
+__device__ __forceinline__ uint32_t ordered_bits(float t) {
+    const uint32_t u = __float_as_uint(t + 0.0f);  // -0 -> +0
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float from_ordered_bits(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ uint32_t make_code(uint32_t ball, uint32_t cat, uint32_t partner) {
+    return (ball << 16) | (cat << 8) | partner;
+}
+__device__ __forceinline__ void offer(unsigned long long* key, float t, uint32_t code) {
+    if (t != t) return;  // a NaN time never wins the reference's strict '<'
+    atomicMin(key, ((unsigned long long)ordered_bits(t) << 32) | code);
+}
+
+// per-ball meta word: kind | rolling << 8 | (lastRail + 1) << 16 | (type + 1) << 24
+__device__ __forceinline__ uint32_t make_meta(int kind, bool rolling, int lastRail, int type) {
+    return (uint32_t)kind | ((uint32_t)rolling << 8) | ((uint32_t)(lastRail + 1) << 16) | ((uint32_t)(type + 1) << 24);
+}
+__device__ __forceinline__ int meta_kind(uint32_t m) { return (int)(m & 0xffu); }
+__device__ __forceinline__ bool meta_rolling(uint32_t m) { return ((m >> 8) & 1u) != 0; }
+__device__ __forceinline__ int meta_last_rail(uint32_t m) { return (int)((m >> 16) & 0xffu) - 1; }
+__device__ __forceinline__ int meta_type(uint32_t m) { return (int)(m >> 24) - 1; }
+__device__ __forceinline__ bool kind_dynamic(int kind) {
+    return kind == K_SHOT || kind == K_MOVING || kind == K_COLLISION || kind == K_RAIL;
+}
+
+struct Candidate {
+    int sIdx;
+    float vx, vy;
+    uint64_t searchCost, baseCost;
+};
+__device__ __forceinline__ Candidate decode_candidate(const LaunchParams& p, int64_t cand) {
+    Candidate c;
+    if (p.src.gridDirs > 0) {
+        const int64_t gid = cand + p.src.firstCandidate;
+        const int64_t perState = (int64_t)p.src.gridDirs * p.src.gridSpeeds;
+        c.sIdx = (int)(gid / perState);
+        const int rem = (int)(gid - (int64_t)c.sIdx * perState);
+        const int k = rem / p.src.gridSpeeds, j = rem - k * p.src.gridSpeeds;
+        const float sp = p.src.speedTable[j];
+        c.vx = sp * p.src.dirTable[2 * k];
+        c.vy = sp * p.src.dirTable[2 * k + 1];
+        c.searchCost = p.src.gridSearchCost;
+        c.baseCost = p.src.stateBaseCost ? p.src.stateBaseCost[c.sIdx] : 0ull;
+    } else {
+        c.sIdx = p.src.stateIdx[cand];
+        c.vx = p.src.vx[cand];
+        c.vy = p.src.vy[cand];
+        c.searchCost = p.src.searchCost[cand];
+        c.baseCost = p.src.baseCost[cand];
+    }
+    return c;
+}
+
+// Appends `pred` threads' values to a global list with one atomicAdd per warp.  Must be called by all 32 lanes.
+__device__ __forceinline__ void warp_append(bool pred, uint32_t value, uint32_t* list, uint32_t* counter) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return;
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == __ffs(m) - 1) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (pred) list[base + __popc(m & ((1u << lane) - 1))] = value;
+}
+
+// rules + simulationCost + result write-out of one finished strike (billiard_search.cpp:1388-1405, 1473-1532;
+// billiard_snooker.cpp:1128-1153); one thread.
+__device__ __noinline__ void finish_strike(const LaunchParams& p, const PipeWorkspace& w, int64_t s, uint32_t flags, int nEvents, float T) {
+    const int NB = p.states.nBalls;
+    const Candidate c = decode_candidate(p, s);
+    const uint32_t expected = p.states.expectedMask[c.sIdx];
+    uint32_t pottedMask = 0;
+    bool cuePotted = false, unexpected = false;
+    double pottingScore = 0.0;
+    for (int b = 0; b < NB; ++b) {   // ascending ball index, as the oracle sums
+        const uint32_t m = w.meta[s * NB + b];
+        if (meta_kind(m) == K_POTTING) {
+            const int type = meta_type(m);
+            pottedMask |= 1u << b;
+            cuePotted |= type == p_rules.cueType;
+            unexpected |= !((expected >> (type & 31)) & 1u);
+            pottingScore += p_rules.score[type];
+        }
+    }
+    uint64_t cost = ~0ull;
+    if (flags & F_COMPLETED) {
+        if (pottedMask != 0 && !cuePotted && !unexpected) flags |= F_VALID;
+        const v2 v0 = mk(c.vx, c.vy);
+        const float velocitySquared = dot(v0, v0);
+        const double velocityCost = (double)(velocitySquared / (5000.0f * 5000.0f));
+        const double pottingCost = 1.0 - (pottingScore < 1.0 ? pottingScore : 1.0);
+        const double wp = 0.5 * pottingCost, wv = 0.5 * velocityCost;
+        const double total = (wp + wv) < 1.0 ? (wp + wv) : 1.0;
+        const double cap = 1.0 * (double)c.searchCost;
+        cost = c.baseCost + (uint64_t)(total * cap);
+    }
+    p.out.cost[s] = cost;
+    p.out.flags[s] = flags | ((uint32_t)nEvents << 8);
+    p.out.potted[s] = pottedMask;
+    p.out.finalTime[s] = T;
+    if (p.out.finalPos) {
+        float2* dst = reinterpret_cast<float2*>(p.out.finalPos) + s * NB;
+        for (int b = 0; b < NB; ++b) {
+            const float4 q = w.pv[s * NB + b];
+            dst[b] = make_float2(q.x, q.y);
+        }
+    }
+    if (p.out.counters) atomicAdd(&p.out.counters[0], (unsigned long long)nEvents);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// init: toInputLayer (billiard_search.cpp:760-795) + System::append of layer 0.  One warp per strike, lane = ball.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) init_kernel(LaunchParams p, PipeWorkspace w) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int NB = p.states.nBalls;
+    const PhysConst pc = p_phys;
+    const int64_t warpsTotal = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
+        const Candidate c = decode_candidate(p, s);
+        int type = -1, kind = K_ABSENT;
+        v2 pos = mk(0.f, 0.f), vel = mk(0.f, 0.f), vn, acc;
+        float nextRolling = -1.0f;
+        if (lane < NB) {
+            type = p.states.type[(int64_t)c.sIdx * NB + lane];
+            if (type >= 0) {
+                const float2 q = reinterpret_cast<const float2*>(p.states.pos)[(int64_t)c.sIdx * NB + lane];
+                pos = mk(q.x, q.y);
+                if (type == p_rules.cueType) {
+                    vel = mk(c.vx, c.vy);
+                    kind = K_SHOT;
+                    nextRolling = time_to_rolling(vel, pc);  // type.cpp:502-506
+                } else {
+                    kind = K_REST;
+                }
+            }
+        }
+        derive_ball(vel, false, pc, &vn, &acc);
+        if (lane < NB) {
+            const int64_t g = s * NB + lane;
+            w.pv[g] = make_float4(pos.x, pos.y, vel.x, vel.y);
+            w.na[g] = make_float4(vn.x, vn.y, acc.x, acc.y);
+            w.nextRolling[g] = nextRolling;
+            w.meta[g] = make_meta(kind, false, -1, type);
+        }
+        const unsigned dynMask = __ballot_sync(FULL, kind == K_SHOT);
+        const unsigned restMask = __ballot_sync(FULL, kind == K_REST);
+        if (kind == K_SHOT) {
+            unsigned long long* key = w.key + s;  // buffer 0
+            offer(key, time_to_stop(acc, vel), make_code(lane, CAT_REST, 0));
+            if (nextRolling >= 0.0f) offer(key, nextRolling, make_code(lane, CAT_ROLLING, 0));
+        }
+        if (lane == 0) {
+            w.dynMask[s] = dynMask; w.restMask[s] = restMask; w.T[s] = 0.0f;
+        }
+        __syncwarp();
+        if (dynMask == 0) {
+            if (lane == 0) finish_strike(p, w, s, F_COMPLETED, 0, 0.0f);
+        } else {
+            if (lane == 0) w.live[atomicAdd(&w.counts[0], 1u)] = (uint32_t)s;
+            const int nd = __popc(dynMask);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&w.counts[1], (uint32_t)nd);
+            base = __shfl_sync(FULL, base, 0);
+            if (kind == K_SHOT) w.dyn[base + __popc(dynMask & ((1u << lane) - 1))] = ((uint32_t)s << 5) | lane;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// items: rails, pockets, ball pairs.
+// ---------------------------------------------------------------------------------------------------------------------
+struct ItemShared {
+    uint32_t code[ITEM_BLOCK * ITEM_IPT];
+    float val[ITEM_BLOCK * ITEM_IPT];
+    int count;
+    uint32_t jobBase;
+};
+
+// Reserves a slot in the CTA's survivor queue for every thread with `surv`; all threads of the warp must call.
+__device__ __forceinline__ int block_slot(bool surv, int* count) {
+    const unsigned m = __ballot_sync(0xffffffffu, surv);
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (m != 0) {
+        if (lane == 0) base = atomicAdd(count, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+    }
+    return base + __popc(m & ((1u << lane) - 1));
+}
+
+__global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeWorkspace w, int round) {
+    __shared__ ItemShared sh;
+    __shared__ RailGeom sRails[MAX_RAILS];
+    __shared__ PocketGeom sPockets[MAX_POCKETS];
+    const int tid = threadIdx.x;
+    const int R = p_table.nRails, P = p_table.nPockets, NB = p.states.nBalls;
+    const uint32_t nDyn = w.counts[4 * round + 1];
+    if (nDyn == 0) return;
+    for (int i = tid; i < R; i += ITEM_BLOCK) sRails[i] = p_table.rails[i];
+    for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p_table.pockets[i];
+    const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
+    unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
+    const float diameter = p_table.diameter;
+    constexpr int TILE = ITEM_BLOCK * ITEM_IPT;
+    __syncthreads();
+
+    // ---- rails.  Stage 1: half-line x shifted segment (billiard_physics.cpp:725-753); stage 2: the quadratic (:181-238)
+    {
+        const int64_t total = (int64_t)nDyn * R;
+        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
+            if (tid == 0) sh.count = 0;
+            __syncthreads();
+            #pragma unroll 1
+            for (int k = 0; k < ITEM_IPT; ++k) {
+                const int64_t idx = base + k * ITEM_BLOCK + tid;
+                bool surv = false;
+                float lam = 0.f;
+                uint32_t code = 0;
+                if (idx < total) {
+                    const uint32_t e = (uint32_t)(idx / R);
+                    const int r = (int)(idx - (int64_t)e * R);
+                    const uint32_t ent = dyn[e];
+                    const int64_t g = (int64_t)(ent >> 5) * NB + (ent & 31u);
+                    if (meta_last_rail(w.meta[g]) != r) {
+                        const float4 st = w.pv[g];
+                        const v2 vel = mk(st.z, st.w);
+                        const RailGeom rg = sRails[r];
+                        float t, u;
+                        if (!is_zero(vel) && line_intersects_line(mk(st.x, st.y), vel, mk(rg.sx, rg.sy), mk(rg.dx, rg.dy), &t, &u) &&
+                            !(t < 0.0f) && !(u < 0.0f || u > 1.0f)) {
+                            surv = true; lam = t; code = (ent << 5) | (uint32_t)r;
+                        }
+                    }
+                }
+                const int slot = block_slot(surv, &sh.count);
+                if (surv) { sh.code[slot] = code; sh.val[slot] = lam; }
+            }
+            __syncthreads();
+            const int cnt = sh.count;
+            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
+                const uint32_t c2 = sh.code[i];
+                const float lambda = sh.val[i];
+                const uint32_t ent = c2 >> 5;
+                const int r = (int)(c2 & 31u), b = (int)(ent & 31u);
+                const int64_t s = ent >> 5, g = s * NB + b;
+                const float4 st = w.pv[g], a4 = w.na[g];
+                const v2 vel = mk(st.z, st.w);
+                const float distance = length(lambda * vel);
+                const float velocity = length(vel);
+                const float a = -length(mk(a4.z, a4.w));
+                float x[2];
+                if (solve_quadratic(0.5f * a, velocity, -distance, x) != 0) offer(key + s, x[0], make_code(b, CAT_RAIL, r));
+            }
+            __syncthreads();
+        }
+    }
+
+    // ---- pockets.  Stage 1: does the travel line reach the pocket circle (discriminant of :584-625); stage 2: the rest
+    {
+        const int64_t total = (int64_t)nDyn * P;
+        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
+            if (tid == 0) sh.count = 0;
+            __syncthreads();
+            #pragma unroll 1
+            for (int k = 0; k < ITEM_IPT; ++k) {
+                const int64_t idx = base + k * ITEM_BLOCK + tid;
+                bool surv = false;
+                uint32_t code = 0;
+                if (idx < total) {
+                    const uint32_t e = (uint32_t)(idx / P);
+                    const int pk = (int)(idx - (int64_t)e * P);
+                    const uint32_t ent = dyn[e];
+                    const int64_t g = (int64_t)(ent >> 5) * NB + (ent & 31u);
+                    const float4 st = w.pv[g], a4 = w.na[g];
+                    if (!is_zero(mk(st.z, st.w))) {
+                        const PocketGeom pg = sPockets[pk];
+                        const v2 delta = mk(st.x, st.y) - mk(pg.x, pg.y);
+                        const float qa = 1;
+                        const float qb = 2 * dot(mk(a4.x, a4.y), delta);
+                        const float qc = dot(delta, delta) - pg.r * pg.r;
+                        const float disc = qb * qb - 4 * qa * qc;
+                        if (!(disc < 0)) { surv = true; code = (ent << 5) | (uint32_t)pk; }
+                    }
+                }
+                const int slot = block_slot(surv, &sh.count);
+                if (surv) sh.code[slot] = code;
+            }
+            __syncthreads();
+            const int cnt = sh.count;
+            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
+                const uint32_t c2 = sh.code[i];
+                const uint32_t ent = c2 >> 5;
+                const int pk = (int)(c2 & 31u), b = (int)(ent & 31u);
+                const int64_t s = ent >> 5, g = s * NB + b;
+                const float4 st = w.pv[g], a4 = w.na[g];
+                float t;
+                if (time_to_pocket(sPockets[pk], mk(st.x, st.y), mk(a4.x, a4.y), mk(st.z, st.w), mk(a4.z, a4.w), &t))
+                    offer(key + s, t, make_code(b, CAT_POCKET, pk));
+            }
+            __syncthreads();
+        }
+    }
+
+    // ---- ball pairs.  Stage 1: the reference's geometric pre-checks (:287-324); stage 2: quantised coefficients
+    //      (:326-337) -> quartic job
+    {
+        const int64_t total = (int64_t)nDyn * NB;
+        uint32_t* jobCount = &w.counts[4 * round + 2];
+        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
+            if (tid == 0) sh.count = 0;
+            __syncthreads();
+            #pragma unroll 1
+            for (int k = 0; k < ITEM_IPT; ++k) {
+                const int64_t idx = base + k * ITEM_BLOCK + tid;
+                bool surv = false;
+                uint32_t code = 0;
+                if (idx < total) {
+                    const uint32_t e = (uint32_t)(idx / NB);
+                    const int o = (int)(idx - (int64_t)e * NB);
+                    const uint32_t ent = dyn[e];
+                    const int64_t s = ent >> 5;
+                    const int b = (int)(ent & 31u);
+                    const bool oStatic = (w.restMask[s] >> o) & 1u, oDyn = (w.dynMask[s] >> o) & 1u;
+                    if (o != b && (oStatic || (oDyn && b < o))) {
+                        const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
+                        const v2 p1 = mk(s1.x, s1.y), v1 = mk(s1.z, s1.w), p2 = mk(s2.x, s2.y), w2 = mk(s2.z, s2.w);
+                        // the reference tests b -> o and, for a dynamic partner, o -> b on o's own turn; the quantised
+                        // coefficients of both orders are identical, so one job covers both
+                        bool pass = collision_precheck(v1, p1, w2, p2, diameter);
+                        if (!pass && oDyn) pass = collision_precheck(w2, p2, v1, p1, diameter);
+                        if (pass) { surv = true; code = (ent << 6) | ((uint32_t)o << 1) | (oStatic ? 0u : 1u); }
+                    }
+                }
+                const int slot = block_slot(surv, &sh.count);
+                if (surv) sh.code[slot] = code;
+            }
+            __syncthreads();
+            const int cnt = sh.count;
+            if (tid == 0 && cnt > 0) sh.jobBase = atomicAdd(jobCount, (uint32_t)cnt);
+            __syncthreads();
+            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
+                const uint32_t c2 = sh.code[i];
+                const uint32_t ent = c2 >> 6;
+                const int o = (int)((c2 >> 1) & 31u), b = (int)(ent & 31u);
+                const int64_t s = ent >> 5;
+                const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
+                const float4 a1 = w.na[s * NB + b], a2 = w.na[s * NB + o];
+                float co[5];
+                collision_coefficients(mk(a1.z, a1.w), mk(s1.z, s1.w), mk(s1.x, s1.y), mk(a2.z, a2.w), mk(s2.z, s2.w),
+                                       mk(s2.x, s2.y), diameter, co);
+                const uint64_t j = (uint64_t)sh.jobBase + i;
+                if (j < w.jobCap) {
+                    #pragma unroll
+                    for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
+                    w.jobCode[j] = c2;
+                } else {  // queue full: solve here (slow, but never wrong)
+                    float t;
+                    if (collision_time_from_coefficients(co, &t))
+                        offer(key + s, t, make_code(b, (c2 & 1u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, o));
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// quartic: one thread per job.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(QUARTIC_BLOCK) quartic_kernel(PipeWorkspace w, int round) {
+    const uint32_t posted = w.counts[4 * round + 2];
+    const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
+    unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
+    for (uint64_t j = (uint64_t)blockIdx.x * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)gridDim.x * QUARTIC_BLOCK) {
+        float co[5];
+        #pragma unroll
+        for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
+        const uint32_t c2 = w.jobCode[j];
+        float t;
+        if (collision_time_from_coefficients(co, &t)) {
+            const uint32_t ent = c2 >> 6;
+            offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 1u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, (c2 >> 1) & 31u));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// apply: the winning event of every live strike, the closed-form advance of every other dynamic ball, next lists.
+// ---------------------------------------------------------------------------------------------------------------------
+struct BallRec {
+    v2 pos, vel, vn, acc;
+    float nextRolling;
+    int kind, lastRail, type;
+    bool rolling;
+};
+__device__ __forceinline__ BallRec load_ball(const PipeWorkspace& w, int64_t g) {
+    BallRec r;
+    const float4 st = w.pv[g], a4 = w.na[g];
+    const uint32_t m = w.meta[g];
+    r.pos = mk(st.x, st.y); r.vel = mk(st.z, st.w); r.vn = mk(a4.x, a4.y); r.acc = mk(a4.z, a4.w);
+    r.nextRolling = w.nextRolling[g];
+    r.kind = meta_kind(m); r.rolling = meta_rolling(m); r.lastRail = meta_last_rail(m); r.type = meta_type(m);
+    return r;
+}
+__device__ __forceinline__ void store_ball(const PipeWorkspace& w, int64_t g, const BallRec& r) {
+    w.pv[g] = make_float4(r.pos.x, r.pos.y, r.vel.x, r.vel.y);
+    w.na[g] = make_float4(r.vn.x, r.vn.y, r.acc.x, r.acc.y);
+    w.nextRolling[g] = r.nextRolling;
+    w.meta[g] = make_meta(r.kind, r.rolling, r.lastRail, r.type);
+}
+// System::append bookkeeping for one ball of the new layer (type.cpp:478-527); `cause` = rail index for K_RAIL
+__device__ __forceinline__ void append_bookkeeping(BallRec& r, float deltaTime, int cause, const PhysConst& pc) {
+    if (r.nextRolling >= 0.0f) { const float nr = r.nextRolling - deltaTime; r.nextRolling = nr > 0.0f ? nr : 0.0f; }
+    if (r.kind == K_COLLISION) {
+        r.lastRail = -1;
+        r.nextRolling = (!r.rolling && !is_zero(r.vel)) ? time_to_rolling(r.vel, pc) : -1.0f;
+    } else if (r.kind == K_REST || r.kind == K_POTTING) {
+        r.nextRolling = -1.0f;
+    } else if (r.kind == K_MOVING) {
+        if (r.rolling) r.nextRolling = -1.0f;
+    } else if (r.kind == K_RAIL) {
+        r.lastRail = cause; r.nextRolling = -1.0f;
+    }
+}
+__device__ __forceinline__ void offer_own(unsigned long long* key, const BallRec& r, int b) {
+    offer(key, time_to_stop(r.acc, r.vel), make_code(b, CAT_REST, 0));
+    if (r.nextRolling >= 0.0f) offer(key, r.nextRolling, make_code(b, CAT_ROLLING, 0));
+}
+
+__global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, PipeWorkspace w, int round) {
+    const int NB = p.states.nBalls;
+    const PhysConst pc = p_phys;
+    const uint32_t nLive = w.counts[4 * round + 0], nDyn = w.counts[4 * round + 1];
+    if (nLive == 0) return;
+    const uint32_t* live = w.live + (size_t)(round & 1) * w.n;
+    uint32_t* liveNext = w.live + (size_t)((round + 1) & 1) * w.n;
+    const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
+    uint32_t* dynNext = w.dyn + (size_t)((round + 1) & 1) * w.dynCap;
+    const unsigned long long* keyCur = w.key + (size_t)(round % 3) * w.n;
+    unsigned long long* keyNext = w.key + (size_t)((round + 1) % 3) * w.n;
+    unsigned long long* keyStale = w.key + (size_t)((round + 2) % 3) * w.n;
+    const float* Tcur = w.T + (size_t)(round & 1) * w.n;
+    float* Tnext = w.T + (size_t)((round + 1) & 1) * w.n;
+    uint32_t* liveCountNext = &w.counts[4 * (round + 1) + 0];
+    uint32_t* dynCountNext = &w.counts[4 * (round + 1) + 1];
+    const bool overflow = round + 1 > MAX_EVENTS;  // billiard_search.cpp:1376-1379 (every live strike has `round` events)
+    const int64_t stride = (int64_t)gridDim.x * APPLY_BLOCK;
+
+    // ---- the event of every live strike (createLayer :1957-1992) ----------------------------------------------------
+    for (int64_t base = (int64_t)blockIdx.x * APPLY_BLOCK; base < nLive; base += stride) {
+        const int64_t idx = base + threadIdx.x;
+        bool appendLive = false, appendA = false, appendB = false;
+        uint32_t entA = 0, entB = 0, sLive = 0;
+        if (idx < nLive) {
+            const int64_t s = live[idx];
+            sLive = (uint32_t)s;
+            const unsigned long long key = keyCur[s];
+            keyStale[s] = ~0ull;
+            const float T = Tcur[s];
+            if (key == ~0ull) {
+                finish_strike(p, w, s, F_NOEVENT, round, T);           // billiard_search.cpp:1464-1467
+            } else if (overflow) {
+                finish_strike(p, w, s, F_OVERFLOW, round, T);
+            } else {
+                const float dt = from_ordered_bits((uint32_t)(key >> 32));
+                const uint32_t code = (uint32_t)key;
+                const int evBall = (int)(code >> 16);
+                const uint32_t cat = (code >> 8) & 0xffu;
+                const int evPartner = (int)(code & 0xffu);
+                const int evType = cat == CAT_REST ? E_REST : cat == CAT_ROLLING ? E_ROLLING : cat == CAT_RAIL ? E_RAIL_COLLISION
+                                 : cat == CAT_POCKET ? E_POTTING : E_BALL_COLLISION;
+                const float newT = T + dt;
+                const float deltaTime = newT - T;  // type.cpp:475
+                Tnext[s] = newT;
+                uint32_t dynMask = w.dynMask[s], restMask = w.restMask[s];
+                const int64_t gA = s * NB + evBall;
+                BallRec A = load_ball(w, gA);
+                const v2 npos = advance_position(A.acc, A.vel, dt, A.pos);
+                const v2 nvel = advance_velocity(A.acc, A.vel, dt);
+                int cause = -1;
+                A.pos = npos;
+                if (evType == E_POTTING) {                 // :1716-1746
+                    A.vel = mk(0.f, 0.f); A.rolling = false; A.kind = K_POTTING;
+                } else if (evType == E_RAIL_COLLISION) {   // :1748-1786
+                    const RailGeom& rg = p_table.rails[evPartner];
+                    A.vel = rail_collision(nvel, mk(rg.nx, rg.ny), pc);
+                    A.rolling = true; A.kind = K_RAIL; cause = evPartner;
+                } else if (evType == E_REST) {             // :1788-1808
+                    A.vel = mk(0.f, 0.f); A.rolling = false; A.kind = K_REST;
+                } else if (evType == E_ROLLING) {          // :1810-1840
+                    A.vel = nvel; A.rolling = true; A.kind = K_MOVING;
+                } else {                                   // :1842-1905 createBallCollisionNodes
+                    const int64_t gB = s * NB + evPartner;
+                    BallRec B = load_ball(w, gB);
+                    const v2 opos = advance_position(B.acc, B.vel, dt, B.pos);
+                    const v2 ovel = advance_velocity(B.acc, B.vel, dt);
+                    v2 o1, o2;
+                    elastic_collision(npos, nvel, opos, ovel, A.rolling, B.rolling, pc, &o1, &o2);
+                    A.vel = o1; A.kind = K_COLLISION;
+                    B.pos = opos; B.vel = o2; B.kind = K_COLLISION;
+                    derive_ball(B.vel, B.rolling, pc, &B.vn, &B.acc);
+                    append_bookkeeping(B, deltaTime, -1, pc);
+                    store_ball(w, gB, B);
+                    offer_own(keyNext + s, B, evPartner);
+                    dynMask |= 1u << evPartner; restMask &= ~(1u << evPartner);
+                    appendB = true; entB = ((uint32_t)s << 5) | (uint32_t)evPartner;
+                }
+                derive_ball(A.vel, A.rolling, pc, &A.vn, &A.acc);
+                append_bookkeeping(A, deltaTime, cause, pc);
+                store_ball(w, gA, A);
+                if (kind_dynamic(A.kind)) {
+                    offer_own(keyNext + s, A, evBall);
+                    appendA = true; entA = ((uint32_t)s << 5) | (uint32_t)evBall;
+                } else {
+                    dynMask &= ~(1u << evBall);
+                    if (A.kind == K_REST) restMask |= 1u << evBall;
+                }
+                w.dynMask[s] = dynMask; w.restMask[s] = restMask;
+                if (p.out.eventLog) {
+                    int a = evBall, b = evPartner;
+                    if (evType == E_BALL_COLLISION && a > b) { const int t = a; a = b; b = t; }
+                    if (evType == E_REST || evType == E_ROLLING) b = -1;
+                    p.out.eventLog[s * 32 + round] = make_int4(evType, a, b, __float_as_int(newT));
+                }
+                if (dynMask == 0) finish_strike(p, w, s, F_COMPLETED, round + 1, newT);
+                else appendLive = true;
+            }
+        }
+        warp_append(appendLive, sLive, liveNext, liveCountNext);
+        warp_append(appendA, entA, dynNext, dynCountNext);
+        warp_append(appendB, entB, dynNext, dynCountNext);
+    }
+
+    // ---- every other dynamic ball: closed-form advance to the new layer (createNodes :1907-1955) ---------------------
+    for (int64_t base = (int64_t)blockIdx.x * APPLY_BLOCK; base < nDyn; base += stride) {
+        const int64_t idx = base + threadIdx.x;
+        bool keep = false;
+        uint32_t ent = 0;
+        if (idx < nDyn && !overflow) {
+            ent = dyn[idx];
+            const int64_t s = ent >> 5;
+            const int b = (int)(ent & 31u);
+            const unsigned long long key = keyCur[s];
+            if (key != ~0ull) {
+                const uint32_t code = (uint32_t)key;
+                const int evBall = (int)(code >> 16);
+                const uint32_t cat = (code >> 8) & 0xffu;
+                const int evPartner = (int)(code & 0xffu);
+                const bool pairEvent = cat == CAT_STATIC_PAIR || cat == CAT_DYNAMIC_PAIR;
+                if (b != evBall && !(pairEvent && b == evPartner)) {
+                    const float dt = from_ordered_bits((uint32_t)(key >> 32));
+                    const float T = Tcur[s];
+                    const float newT = T + dt;
+                    const float deltaTime = newT - T;
+                    const int64_t g = s * NB + b;
+                    BallRec r = load_ball(w, g);
+                    const v2 nv = advance_velocity(r.acc, r.vel, dt);
+                    r.pos = advance_position(r.acc, r.vel, dt, r.pos);
+                    r.vel = nv; r.kind = K_MOVING;
+                    derive_ball(r.vel, r.rolling, pc, &r.vn, &r.acc);
+                    append_bookkeeping(r, deltaTime, -1, pc);
+                    store_ball(w, g, r);
+                    offer_own(keyNext + s, r, b);
+                    keep = true;
+                }
+            }
+        }
+        warp_append(keep, ent, dynNext, dynCountNext);
+    }
+}
+
+// work counters from the per-round list sizes: [1] pair items [2] quartics [3] rail items [4] pocket items
+__global__ void counters_kernel(LaunchParams p, PipeWorkspace w) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long pairs = 0, quartics = 0, rails = 0, pockets = 0;
+    for (int r = 0; r < ROUNDS; ++r) {
+        const unsigned long long d = w.counts[4 * r + 1];
+        if (w.counts[4 * r + 0] == 0) continue;
+        pairs += d * p.states.nBalls; rails += d * p_table.nRails; pockets += d * p_table.nPockets;
+        quartics += w.counts[4 * r + 2];
+    }
+    p.out.counters[1] += pairs; p.out.counters[2] += quartics; p.out.counters[3] += rails; p.out.counters[4] += pockets;
+}
+
+}  // namespace
+
+void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream) {
+    PhysConst pc = phys_const();
+    cudaMemcpyToSymbolAsync(p_table, &table, sizeof(TableGeom), 0, cudaMemcpyHostToDevice, stream);
+    cudaMemcpyToSymbolAsync(p_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
+    cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
+}
+
+size_t pipeline_workspace_bytes(int64_t n, int nBalls, PipeWorkspace* layout) {
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    PipeWorkspace w{};
+    w.n = n;
+    w.dynCap = (size_t)n * nBalls;
+    w.jobCap = (size_t)n * PIPE_JOBS_PER_STRIKE;
+    if (w.jobCap < 4096) w.jobCap = 4096;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align(bytes); return o; };
+    const size_t nb = (size_t)n * nBalls;
+    const size_t oPv = take(nb * sizeof(float4)), oNa = take(nb * sizeof(float4)), oNr = take(nb * sizeof(float));
+    const size_t oMeta = take(nb * sizeof(uint32_t));
+    const size_t oKey = take((size_t)3 * n * sizeof(unsigned long long));
+    const size_t oT = take((size_t)2 * n * sizeof(float));
+    const size_t oDm = take((size_t)n * sizeof(uint32_t)), oRm = take((size_t)n * sizeof(uint32_t));
+    const size_t oLive = take((size_t)2 * n * sizeof(uint32_t));
+    const size_t oDyn = take((size_t)2 * w.dynCap * sizeof(uint32_t));
+    const size_t oCounts = take((size_t)4 * (ROUNDS + 1) * sizeof(uint32_t));
+    const size_t oCo = take((size_t)5 * w.jobCap * sizeof(float)), oCode = take(w.jobCap * sizeof(uint32_t));
+    if (layout) {
+        unsigned char* b = reinterpret_cast<unsigned char*>(layout->base);
+        w.base = layout->base;
+        w.pv = reinterpret_cast<float4*>(b + oPv); w.na = reinterpret_cast<float4*>(b + oNa);
+        w.nextRolling = reinterpret_cast<float*>(b + oNr); w.meta = reinterpret_cast<uint32_t*>(b + oMeta);
+        w.key = reinterpret_cast<unsigned long long*>(b + oKey); w.T = reinterpret_cast<float*>(b + oT);
+        w.dynMask = reinterpret_cast<uint32_t*>(b + oDm); w.restMask = reinterpret_cast<uint32_t*>(b + oRm);
+        w.live = reinterpret_cast<uint32_t*>(b + oLive); w.dyn = reinterpret_cast<uint32_t*>(b + oDyn);
+        w.counts = reinterpret_cast<uint32_t*>(b + oCounts);
+        w.jobCo = reinterpret_cast<float*>(b + oCo); w.jobCode = reinterpret_cast<uint32_t*>(b + oCode);
+        *layout = w;
+    }
+    return off;
+}
+
+int pipeline_launch_count() { return 1 + 3 * ROUNDS; }
+
+// One launch of the batch path over p.nCand <= PIPE_MAX_STRIKES strikes.  `w` must have been laid out for >= p.nCand.
+cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& wsIn, int sms, cudaStream_t stream) {
+    if (p.nCand <= 0) return cudaSuccess;
+    PipeWorkspace w = wsIn;
+    cudaError_t e;
+    if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(w.counts, 0, (size_t)4 * (ROUNDS + 1) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    const int64_t initBlocks = (p.nCand + 7) / 8;
+    init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
+    for (int r = 0; r < ROUNDS; ++r) {
+        items_kernel<<<sms * 4, ITEM_BLOCK, 0, stream>>>(p, w, r);
+        quartic_kernel<<<sms * 4, QUARTIC_BLOCK, 0, stream>>>(w, r);
+        apply_kernel<<<sms * 4, APPLY_BLOCK, 0, stream>>>(p, w, r);
+    }
+    if (p.out.counters) counters_kernel<<<1, 32, 0, stream>>>(p, w);
+    return cudaGetLastError();
+}
+
+}  // namespace bcu
