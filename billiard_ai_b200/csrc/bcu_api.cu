@@ -70,6 +70,8 @@ struct bcu_engine {
     DevBuf<unsigned long long> dCounters, dNextCand;
     DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
     int sms = 148;
+    int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
+    uint32_t* hOverflow = nullptr;   // pinned
     int kernelVersion = 3;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
     // top-k
     DevBuf<unsigned char> dTopkScratch;
@@ -238,6 +240,7 @@ void bcu_destroy(bcu_engine* e) {
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
     if (e->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->ncclComm);
+    if (e->hOverflow) cudaFreeHost(e->hOverflow);
     if (e->evT0) cudaEventDestroy(e->evT0);
     if (e->evT1) cudaEventDestroy(e->evT1);
     if (e->evStart) cudaEventDestroy(e->evStart);
@@ -316,10 +319,7 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
     } else {
         // batch path: chunks of at most PIPE_MAX_STRIKES strikes through the event-synchronous pipeline
         const int64_t chunk = p.nCand < PIPE_MAX_STRIKES ? p.nCand : PIPE_MAX_STRIKES;
-        PipeWorkspace ws{};
-        CK(e->dPipeWs.reserve(pipeline_workspace_bytes(chunk, p.states.nBalls, nullptr)));
-        ws.base = e->dPipeWs.p;
-        pipeline_workspace_bytes(chunk, p.states.nBalls, &ws);
+        if (!e->hOverflow) CK(cudaMallocHost(&e->hOverflow, sizeof(uint32_t)));
         for (int64_t off = 0; off < p.nCand; off += chunk) {
             LaunchParams q = p;
             q.nCand = p.nCand - off < chunk ? p.nCand - off : chunk;
@@ -331,8 +331,20 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
             q.out.cost += off; q.out.flags += off; q.out.potted += off; q.out.finalTime += off;
             if (q.out.finalPos) q.out.finalPos += (size_t)off * p.states.nBalls * 2;
             if (q.out.eventLog) q.out.eventLog += (size_t)off * 32;
-            CK(launch_pipeline(q, ws, e->sms, e->stream));
-            e->launches += pipeline_launch_count();
+            for (;;) {
+                PipeWorkspace ws{};
+                CK(e->dPipeWs.reserve(pipeline_workspace_bytes(chunk, p.states.nBalls, e->jobsPerStrike, nullptr)));
+                ws.base = e->dPipeWs.p;
+                pipeline_workspace_bytes(chunk, p.states.nBalls, e->jobsPerStrike, &ws);
+                CK(launch_pipeline(q, ws, e->sms, e->stream));
+                e->launches += pipeline_launch_count();
+                // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
+                CK(cudaMemcpyAsync(e->hOverflow, pipeline_overflow_flag(ws), sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+                CK(cudaStreamSynchronize(e->stream));
+                if (*e->hOverflow == 0) break;
+                if (e->jobsPerStrike >= 1024) return fail(e, BCU_ERR_STATE, "quartic job queue overflow");
+                e->jobsPerStrike *= 2;
+            }
         }
     }
     CK(cudaEventRecord(e->evStop, e->stream));

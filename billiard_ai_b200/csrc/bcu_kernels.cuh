@@ -54,7 +54,8 @@ struct LaunchParams {
 
 // ---- K1 v3, the event-synchronous batch pipeline (bcu_pipeline.cu) ----------------------------------------------
 constexpr int64_t PIPE_MAX_STRIKES = 1 << 20;   // per launch; larger batches are chunked by the caller
-constexpr int PIPE_JOBS_PER_STRIKE = 16;         // quartic-queue capacity per strike and round (overflow is solved in place)
+constexpr int PIPE_JOBS_PER_STRIKE = 8;          // initial quartic-queue capacity per strike and round; on overflow the
+                                                 // launch raises a flag and the host doubles the queue and re-runs it
 struct PipeWorkspace {
     void* base;
     int64_t n;                 // strikes this layout was made for
@@ -75,9 +76,10 @@ struct PipeWorkspace {
     uint32_t* counts;          // [rounds + 1][4] {live, dynamic balls, quartic jobs, -}
     // quartic jobs of the round
     float* jobCo;              // [5][jobCap]
-    uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner << 1 | partner is dynamic
+    uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner
 };
-size_t pipeline_workspace_bytes(int64_t n, int nBalls, PipeWorkspace* layout);
+size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
+const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
 void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
 cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& w, int sms, cudaStream_t stream);
 int pipeline_launch_count();

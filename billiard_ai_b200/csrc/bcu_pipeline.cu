@@ -8,21 +8,21 @@
 // All strikes of a launch advance one event per ROUND (the reference's event loop, billiard_search.cpp:1370-1381,
 // turned inside out).  State lives in HBM/L2 as structure-of-arrays; per round three kernels run on the stream:
 //
-//   items_kernel    one thread per (dynamic ball x rail | pocket | partner ball) item of every live strike
-//                   (nextRailCollision :1639-1682, nextPocketCollision :1684-1714, nextBallCollision :1603-1637).
-//                   A cheap first stage filters; survivors are compacted per CTA in shared memory so the second
+//   items_kernel    one thread per dynamic ball of every live strike walks its rails, pockets and partner balls
+//                   (nextRailCollision :1639-1682, nextPocketCollision :1684-1714, nextBallCollision :1603-1637)
+//                   with the cheap first-stage tests; survivors are compacted per CTA in shared memory so the second
 //                   stages (rail / pocket quadratics, quantised quartic coefficients) run on dense threads.
 //                   Rail / pocket times go to the strike's 64-bit (time, evaluation order) key with atomicMin -- the
 //                   reference's strict-'<' first-evaluated-wins choice (:2002-2013); ball pairs become quartic jobs
 //                   in a global queue.
 //   quartic_kernel  one thread per job: the FP64 complex closed-form quartic (billiard_physics.cpp:470-560).
 //   apply_kernel    one thread per live strike applies the winning event (createLayer :1957-1992, System::append
-//                   type.cpp:467-531), finishes strikes that reached their final layer (rules + simulationCost
-//                   :1388-1405, :1473-1532) and one thread per other dynamic ball advances it in closed form; both
+//                   type.cpp:467-531) and one thread per other dynamic ball advances it in closed form; both
 //                   offer the rest / rolling times of the next round (nextBallInRest :1590, nextRolling :1575) and
 //                   build the next round's stream-compacted lists of live strikes and dynamic balls.
 //
-// Keys are triple-buffered by round (read r%3, offered (r+1)%3, reset (r+2)%3) and layer times double-buffered, so no
+// After the last round finish_kernel (one warp per strike) evaluates the rules and simulationCost (:1388-1405, :1473-1532)
+// and writes the results.  Keys are triple-buffered by round (read r%3, offered (r+1)%3, reset (r+2)%3) and layer times double-buffered, so no
 // kernel reads a word another thread of the same launch writes.
 #include <cuda_runtime.h>
 
@@ -38,8 +38,6 @@ __constant__ RulesData p_rules;
 __constant__ PhysConst p_phys;
 
 constexpr int ROUNDS = MAX_EVENTS + 1;  // round r applies event r+1; round MAX_EVENTS only flags overflow
-constexpr int ITEM_BLOCK = 256;
-constexpr int ITEM_IPT = 4;            // stage-1 items per thread per tile
 constexpr int QUARTIC_BLOCK = 128;
 constexpr int APPLY_BLOCK = 256;
 
@@ -111,49 +109,11 @@ __device__ __forceinline__ void warp_append(bool pred, uint32_t value, uint32_t*
     if (pred) list[base + __popc(m & ((1u << lane) - 1))] = value;
 }
 
-// rules + simulationCost + result write-out of one finished strike (billiard_search.cpp:1388-1405, 1473-1532;
-// billiard_snooker.cpp:1128-1153); one thread.
-__device__ __noinline__ void finish_strike(const LaunchParams& p, const PipeWorkspace& w, int64_t s, uint32_t flags, int nEvents, float T) {
-    const int NB = p.states.nBalls;
-    const Candidate c = decode_candidate(p, s);
-    const uint32_t expected = p.states.expectedMask[c.sIdx];
-    uint32_t pottedMask = 0;
-    bool cuePotted = false, unexpected = false;
-    double pottingScore = 0.0;
-    for (int b = 0; b < NB; ++b) {   // ascending ball index, as the oracle sums
-        const uint32_t m = w.meta[s * NB + b];
-        if (meta_kind(m) == K_POTTING) {
-            const int type = meta_type(m);
-            pottedMask |= 1u << b;
-            cuePotted |= type == p_rules.cueType;
-            unexpected |= !((expected >> (type & 31)) & 1u);
-            pottingScore += p_rules.score[type];
-        }
-    }
-    uint64_t cost = ~0ull;
-    if (flags & F_COMPLETED) {
-        if (pottedMask != 0 && !cuePotted && !unexpected) flags |= F_VALID;
-        const v2 v0 = mk(c.vx, c.vy);
-        const float velocitySquared = dot(v0, v0);
-        const double velocityCost = (double)(velocitySquared / (5000.0f * 5000.0f));
-        const double pottingCost = 1.0 - (pottingScore < 1.0 ? pottingScore : 1.0);
-        const double wp = 0.5 * pottingCost, wv = 0.5 * velocityCost;
-        const double total = (wp + wv) < 1.0 ? (wp + wv) : 1.0;
-        const double cap = 1.0 * (double)c.searchCost;
-        cost = c.baseCost + (uint64_t)(total * cap);
-    }
-    p.out.cost[s] = cost;
+// A strike that reached its last layer is only MARKED here (flags | nEvents << 8, final layer time); the rules, the cost
+// and the result write-out are done for all strikes at once by finish_kernel.
+__device__ __forceinline__ void mark_finished(const LaunchParams& p, int64_t s, uint32_t flags, int nEvents, float T) {
     p.out.flags[s] = flags | ((uint32_t)nEvents << 8);
-    p.out.potted[s] = pottedMask;
     p.out.finalTime[s] = T;
-    if (p.out.finalPos) {
-        float2* dst = reinterpret_cast<float2*>(p.out.finalPos) + s * NB;
-        for (int b = 0; b < NB; ++b) {
-            const float4 q = w.pv[s * NB + b];
-            dst[b] = make_float2(q.x, q.y);
-        }
-    }
-    if (p.out.counters) atomicAdd(&p.out.counters[0], (unsigned long long)nEvents);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -204,7 +164,7 @@ __global__ void __launch_bounds__(256) init_kernel(LaunchParams p, PipeWorkspace
         }
         __syncwarp();
         if (dynMask == 0) {
-            if (lane == 0) finish_strike(p, w, s, F_COMPLETED, 0, 0.0f);
+            if (lane == 0) mark_finished(p, s, F_COMPLETED, 0, 0.0f);
         } else {
             if (lane == 0) w.live[atomicAdd(&w.counts[0], 1u)] = (uint32_t)s;
             const int nd = __popc(dynMask);
@@ -216,203 +176,7 @@ __global__ void __launch_bounds__(256) init_kernel(LaunchParams p, PipeWorkspace
     }
 }
 
-// ---------------------------------------------------------------------------------------------------------------------
-// items: rails, pockets, ball pairs.
-// ---------------------------------------------------------------------------------------------------------------------
-struct ItemShared {
-    uint32_t code[ITEM_BLOCK * ITEM_IPT];
-    float val[ITEM_BLOCK * ITEM_IPT];
-    int count;
-    uint32_t jobBase;
-};
-
-// Reserves a slot in the CTA's survivor queue for every thread with `surv`; all threads of the warp must call.
-__device__ __forceinline__ int block_slot(bool surv, int* count) {
-    const unsigned m = __ballot_sync(0xffffffffu, surv);
-    const int lane = threadIdx.x & 31;
-    int base = 0;
-    if (m != 0) {
-        if (lane == 0) base = atomicAdd(count, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, 0);
-    }
-    return base + __popc(m & ((1u << lane) - 1));
-}
-
-__global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeWorkspace w, int round) {
-    __shared__ ItemShared sh;
-    __shared__ RailGeom sRails[MAX_RAILS];
-    __shared__ PocketGeom sPockets[MAX_POCKETS];
-    const int tid = threadIdx.x;
-    const int R = p_table.nRails, P = p_table.nPockets, NB = p.states.nBalls;
-    const uint32_t nDyn = w.counts[4 * round + 1];
-    if (nDyn == 0) return;
-    for (int i = tid; i < R; i += ITEM_BLOCK) sRails[i] = p_table.rails[i];
-    for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p_table.pockets[i];
-    const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
-    unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
-    const float diameter = p_table.diameter;
-    constexpr int TILE = ITEM_BLOCK * ITEM_IPT;
-    __syncthreads();
-
-    // ---- rails.  Stage 1: half-line x shifted segment (billiard_physics.cpp:725-753); stage 2: the quadratic (:181-238)
-    {
-        const int64_t total = (int64_t)nDyn * R;
-        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
-            if (tid == 0) sh.count = 0;
-            __syncthreads();
-            #pragma unroll 1
-            for (int k = 0; k < ITEM_IPT; ++k) {
-                const int64_t idx = base + k * ITEM_BLOCK + tid;
-                bool surv = false;
-                float lam = 0.f;
-                uint32_t code = 0;
-                if (idx < total) {
-                    const uint32_t e = (uint32_t)(idx / R);
-                    const int r = (int)(idx - (int64_t)e * R);
-                    const uint32_t ent = dyn[e];
-                    const int64_t g = (int64_t)(ent >> 5) * NB + (ent & 31u);
-                    if (meta_last_rail(w.meta[g]) != r) {
-                        const float4 st = w.pv[g];
-                        const v2 vel = mk(st.z, st.w);
-                        const RailGeom rg = sRails[r];
-                        float t, u;
-                        if (!is_zero(vel) && line_intersects_line(mk(st.x, st.y), vel, mk(rg.sx, rg.sy), mk(rg.dx, rg.dy), &t, &u) &&
-                            !(t < 0.0f) && !(u < 0.0f || u > 1.0f)) {
-                            surv = true; lam = t; code = (ent << 5) | (uint32_t)r;
-                        }
-                    }
-                }
-                const int slot = block_slot(surv, &sh.count);
-                if (surv) { sh.code[slot] = code; sh.val[slot] = lam; }
-            }
-            __syncthreads();
-            const int cnt = sh.count;
-            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
-                const uint32_t c2 = sh.code[i];
-                const float lambda = sh.val[i];
-                const uint32_t ent = c2 >> 5;
-                const int r = (int)(c2 & 31u), b = (int)(ent & 31u);
-                const int64_t s = ent >> 5, g = s * NB + b;
-                const float4 st = w.pv[g], a4 = w.na[g];
-                const v2 vel = mk(st.z, st.w);
-                const float distance = length(lambda * vel);
-                const float velocity = length(vel);
-                const float a = -length(mk(a4.z, a4.w));
-                float x[2];
-                if (solve_quadratic(0.5f * a, velocity, -distance, x) != 0) offer(key + s, x[0], make_code(b, CAT_RAIL, r));
-            }
-            __syncthreads();
-        }
-    }
-
-    // ---- pockets.  Stage 1: does the travel line reach the pocket circle (discriminant of :584-625); stage 2: the rest
-    {
-        const int64_t total = (int64_t)nDyn * P;
-        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
-            if (tid == 0) sh.count = 0;
-            __syncthreads();
-            #pragma unroll 1
-            for (int k = 0; k < ITEM_IPT; ++k) {
-                const int64_t idx = base + k * ITEM_BLOCK + tid;
-                bool surv = false;
-                uint32_t code = 0;
-                if (idx < total) {
-                    const uint32_t e = (uint32_t)(idx / P);
-                    const int pk = (int)(idx - (int64_t)e * P);
-                    const uint32_t ent = dyn[e];
-                    const int64_t g = (int64_t)(ent >> 5) * NB + (ent & 31u);
-                    const float4 st = w.pv[g], a4 = w.na[g];
-                    if (!is_zero(mk(st.z, st.w))) {
-                        const PocketGeom pg = sPockets[pk];
-                        const v2 delta = mk(st.x, st.y) - mk(pg.x, pg.y);
-                        const float qa = 1;
-                        const float qb = 2 * dot(mk(a4.x, a4.y), delta);
-                        const float qc = dot(delta, delta) - pg.r * pg.r;
-                        const float disc = qb * qb - 4 * qa * qc;
-                        if (!(disc < 0)) { surv = true; code = (ent << 5) | (uint32_t)pk; }
-                    }
-                }
-                const int slot = block_slot(surv, &sh.count);
-                if (surv) sh.code[slot] = code;
-            }
-            __syncthreads();
-            const int cnt = sh.count;
-            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
-                const uint32_t c2 = sh.code[i];
-                const uint32_t ent = c2 >> 5;
-                const int pk = (int)(c2 & 31u), b = (int)(ent & 31u);
-                const int64_t s = ent >> 5, g = s * NB + b;
-                const float4 st = w.pv[g], a4 = w.na[g];
-                float t;
-                if (time_to_pocket(sPockets[pk], mk(st.x, st.y), mk(a4.x, a4.y), mk(st.z, st.w), mk(a4.z, a4.w), &t))
-                    offer(key + s, t, make_code(b, CAT_POCKET, pk));
-            }
-            __syncthreads();
-        }
-    }
-
-    // ---- ball pairs.  Stage 1: the reference's geometric pre-checks (:287-324); stage 2: quantised coefficients
-    //      (:326-337) -> quartic job
-    {
-        const int64_t total = (int64_t)nDyn * NB;
-        uint32_t* jobCount = &w.counts[4 * round + 2];
-        for (int64_t base = (int64_t)blockIdx.x * TILE; base < total; base += (int64_t)gridDim.x * TILE) {
-            if (tid == 0) sh.count = 0;
-            __syncthreads();
-            #pragma unroll 1
-            for (int k = 0; k < ITEM_IPT; ++k) {
-                const int64_t idx = base + k * ITEM_BLOCK + tid;
-                bool surv = false;
-                uint32_t code = 0;
-                if (idx < total) {
-                    const uint32_t e = (uint32_t)(idx / NB);
-                    const int o = (int)(idx - (int64_t)e * NB);
-                    const uint32_t ent = dyn[e];
-                    const int64_t s = ent >> 5;
-                    const int b = (int)(ent & 31u);
-                    const bool oStatic = (w.restMask[s] >> o) & 1u, oDyn = (w.dynMask[s] >> o) & 1u;
-                    if (o != b && (oStatic || (oDyn && b < o))) {
-                        const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
-                        const v2 p1 = mk(s1.x, s1.y), v1 = mk(s1.z, s1.w), p2 = mk(s2.x, s2.y), w2 = mk(s2.z, s2.w);
-                        // the reference tests b -> o and, for a dynamic partner, o -> b on o's own turn; the quantised
-                        // coefficients of both orders are identical, so one job covers both
-                        bool pass = collision_precheck(v1, p1, w2, p2, diameter);
-                        if (!pass && oDyn) pass = collision_precheck(w2, p2, v1, p1, diameter);
-                        if (pass) { surv = true; code = (ent << 6) | ((uint32_t)o << 1) | (oStatic ? 0u : 1u); }
-                    }
-                }
-                const int slot = block_slot(surv, &sh.count);
-                if (surv) sh.code[slot] = code;
-            }
-            __syncthreads();
-            const int cnt = sh.count;
-            if (tid == 0 && cnt > 0) sh.jobBase = atomicAdd(jobCount, (uint32_t)cnt);
-            __syncthreads();
-            for (int i = tid; i < cnt; i += ITEM_BLOCK) {
-                const uint32_t c2 = sh.code[i];
-                const uint32_t ent = c2 >> 6;
-                const int o = (int)((c2 >> 1) & 31u), b = (int)(ent & 31u);
-                const int64_t s = ent >> 5;
-                const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
-                const float4 a1 = w.na[s * NB + b], a2 = w.na[s * NB + o];
-                float co[5];
-                collision_coefficients(mk(a1.z, a1.w), mk(s1.z, s1.w), mk(s1.x, s1.y), mk(a2.z, a2.w), mk(s2.z, s2.w),
-                                       mk(s2.x, s2.y), diameter, co);
-                const uint64_t j = (uint64_t)sh.jobBase + i;
-                if (j < w.jobCap) {
-                    #pragma unroll
-                    for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
-                    w.jobCode[j] = c2;
-                } else {  // queue full: solve here (slow, but never wrong)
-                    float t;
-                    if (collision_time_from_coefficients(co, &t))
-                        offer(key + s, t, make_code(b, (c2 & 1u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, o));
-                }
-            }
-            __syncthreads();
-        }
-    }
-}
+#include "bcu_items.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------------
 // quartic: one thread per job.
@@ -429,7 +193,7 @@ __global__ void __launch_bounds__(QUARTIC_BLOCK) quartic_kernel(PipeWorkspace w,
         float t;
         if (collision_time_from_coefficients(co, &t)) {
             const uint32_t ent = c2 >> 6;
-            offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 1u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, (c2 >> 1) & 31u));
+            offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
         }
     }
 }
@@ -508,9 +272,9 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
             keyStale[s] = ~0ull;
             const float T = Tcur[s];
             if (key == ~0ull) {
-                finish_strike(p, w, s, F_NOEVENT, round, T);           // billiard_search.cpp:1464-1467
+                mark_finished(p, s, F_NOEVENT, round, T);              // billiard_search.cpp:1464-1467
             } else if (overflow) {
-                finish_strike(p, w, s, F_OVERFLOW, round, T);
+                mark_finished(p, s, F_OVERFLOW, round, T);
             } else {
                 const float dt = from_ordered_bits((uint32_t)(key >> 32));
                 const uint32_t code = (uint32_t)key;
@@ -572,7 +336,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                     if (evType == E_REST || evType == E_ROLLING) b = -1;
                     p.out.eventLog[s * 32 + round] = make_int4(evType, a, b, __float_as_int(newT));
                 }
-                if (dynMask == 0) finish_strike(p, w, s, F_COMPLETED, round + 1, newT);
+                if (dynMask == 0) mark_finished(p, s, F_COMPLETED, round + 1, newT);
                 else appendLive = true;
             }
         }
@@ -619,6 +383,56 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
     }
 }
 
+// rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
+// One warp per strike, lane = ball.
+__global__ void __launch_bounds__(256) finish_kernel(LaunchParams p, PipeWorkspace w) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int NB = p.states.nBalls;
+    const int64_t warpsTotal = (int64_t)gridDim.x * (blockDim.x >> 5);
+    unsigned long long events = 0;
+    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
+        const Candidate c = decode_candidate(p, s);
+        uint32_t flags = p.out.flags[s];
+        int kind = K_ABSENT, type = -1;
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lane < NB) {
+            const uint32_t m = w.meta[s * NB + lane];
+            kind = meta_kind(m); type = meta_type(m);
+            q = w.pv[s * NB + lane];
+        }
+        const unsigned pottedMask = __ballot_sync(FULL, kind == K_POTTING);
+        const unsigned cuePotted = __ballot_sync(FULL, kind == K_POTTING && type == p_rules.cueType);
+        const uint32_t expected = p.states.expectedMask[c.sIdx];
+        const unsigned unexpected = __ballot_sync(FULL, kind == K_POTTING && !((expected >> (type & 31)) & 1u));
+        uint64_t cost = ~0ull;
+        if (flags & F_COMPLETED) {
+            if (pottedMask != 0 && cuePotted == 0 && unexpected == 0) flags |= F_VALID;
+            double pottingScore = 0.0;
+            for (unsigned m = pottedMask; m; m &= m - 1) {   // ascending ball index, as the oracle sums
+                const int b = __ffs(m) - 1;
+                pottingScore += p_rules.score[__shfl_sync(FULL, type, b)];
+            }
+            const v2 v0 = mk(c.vx, c.vy);
+            const float velocitySquared = dot(v0, v0);
+            const double velocityCost = (double)(velocitySquared / (5000.0f * 5000.0f));
+            const double pottingCost = 1.0 - (pottingScore < 1.0 ? pottingScore : 1.0);
+            const double wp = 0.5 * pottingCost, wv = 0.5 * velocityCost;
+            const double total = (wp + wv) < 1.0 ? (wp + wv) : 1.0;
+            const double cap = 1.0 * (double)c.searchCost;
+            cost = c.baseCost + (uint64_t)(total * cap);
+        }
+        if (lane == 0) {
+            p.out.cost[s] = cost;
+            p.out.flags[s] = flags;
+            p.out.potted[s] = pottedMask;
+            events += (flags >> 8) & 0xffu;
+        }
+        if (p.out.finalPos && lane < NB) reinterpret_cast<float2*>(p.out.finalPos)[s * NB + lane] = make_float2(q.x, q.y);
+    }
+    if (p.out.counters && lane == 0 && events) atomicAdd(&p.out.counters[0], events);
+}
+
 // work counters from the per-round list sizes: [1] pair items [2] quartics [3] rail items [4] pocket items
 __global__ void counters_kernel(LaunchParams p, PipeWorkspace w) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -634,19 +448,24 @@ __global__ void counters_kernel(LaunchParams p, PipeWorkspace w) {
 
 }  // namespace
 
+static int g_nRails = MAX_RAILS, g_nPockets = MAX_POCKETS;
+
 void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream) {
     PhysConst pc = phys_const();
+    g_nRails = table.nRails; g_nPockets = table.nPockets;
     cudaMemcpyToSymbolAsync(p_table, &table, sizeof(TableGeom), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(p_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
 }
 
-size_t pipeline_workspace_bytes(int64_t n, int nBalls, PipeWorkspace* layout) {
+const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w) { return w.counts + 4 * ROUNDS + 3; }
+
+size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout) {
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     PipeWorkspace w{};
     w.n = n;
     w.dynCap = (size_t)n * nBalls;
-    w.jobCap = (size_t)n * PIPE_JOBS_PER_STRIKE;
+    w.jobCap = (size_t)n * jobsPerStrike;
     if (w.jobCap < 4096) w.jobCap = 4096;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align(bytes); return o; };
@@ -675,7 +494,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, PipeWorkspace* layout) {
     return off;
 }
 
-int pipeline_launch_count() { return 1 + 3 * ROUNDS; }
+int pipeline_launch_count() { return 2 + 3 * ROUNDS; }
 
 // One launch of the batch path over p.nCand <= PIPE_MAX_STRIKES strikes.  `w` must have been laid out for >= p.nCand.
 cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& wsIn, int sms, cudaStream_t stream) {
@@ -684,13 +503,21 @@ cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& wsIn, in
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(w.counts, 0, (size_t)4 * (ROUNDS + 1) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * p.states.nBalls) * sizeof(uint32_t);
+    static bool attrSet = false;
+    if (!attrSet) {
+        cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(ITEM_BLOCK * (MAX_RAILS + MAX_POCKETS + 2 * MAX_BALLS) * sizeof(uint32_t)));
+        attrSet = true;
+    }
     const int64_t initBlocks = (p.nCand + 7) / 8;
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     for (int r = 0; r < ROUNDS; ++r) {
-        items_kernel<<<sms * 4, ITEM_BLOCK, 0, stream>>>(p, w, r);
+        items_kernel<<<sms * 8, ITEM_BLOCK, itemSmem, stream>>>(p, w, r);
         quartic_kernel<<<sms * 4, QUARTIC_BLOCK, 0, stream>>>(w, r);
         apply_kernel<<<sms * 4, APPLY_BLOCK, 0, stream>>>(p, w, r);
     }
+    finish_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     if (p.out.counters) counters_kernel<<<1, 32, 0, stream>>>(p, w);
     return cudaGetLastError();
 }
