@@ -21,7 +21,9 @@ struct ItemCounts {
 };
 
 // Appends the set bits of `mask` (as base | bit index) to a shared-memory queue; all 32 lanes must call.
-__device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint32_t* queue, int* counter) {
+// Queue entries are 16 bit: thread-in-tile << 5 | item (pairs: thread << 6 | partner is dynamic << 5 | partner); the
+// thread's list entry (strike << 5 | ball) is looked up in sEnt[].
+__device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint16_t* queue, int* counter) {
     const int lane = threadIdx.x & 31;
     const int cnt = __popc(mask);
     int incl = cnt;
@@ -38,13 +40,15 @@ __device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint32_t
     while (mask) {
         const int bit = __ffs(mask) - 1;
         mask &= mask - 1;
-        queue[at++] = base | (uint32_t)bit;
+        queue[at++] = (uint16_t)(base | (uint32_t)bit);
     }
 }
 
 __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeWorkspace w, int round) {
-    extern __shared__ uint32_t smemQ[];
+    extern __shared__ uint16_t smemQ[];
     __shared__ ItemCounts cnt;
+    __shared__ uint32_t sEnt[ITEM_BLOCK];
+    __shared__ uint32_t sJobBase;
     __shared__ RailGeom sRails[MAX_RAILS];
     __shared__ float sDetQV[MAX_RAILS];
     __shared__ PocketGeom sPockets[MAX_POCKETS];
@@ -59,10 +63,11 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
         sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
     }
     for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p_table.pockets[i];
-    uint32_t* qRails = smemQ;
-    uint32_t* qPockets = qRails + ITEM_BLOCK * R;
-    uint32_t* qPairs = qPockets + ITEM_BLOCK * P;
-    uint32_t* qDyn = qPairs + ITEM_BLOCK * NB;
+    uint16_t* qRails = smemQ;
+    uint16_t* qPockets = qRails + ITEM_BLOCK * R;
+    uint16_t* qPairs = qPockets + ITEM_BLOCK * P;
+    uint16_t* qDyn = qPairs + ITEM_BLOCK * NB;
+    const int64_t n = w.n;
     const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
     unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
     uint32_t* jobCount = &w.counts[4 * round + 2];
@@ -80,11 +85,11 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
             ent = dyn[e];
             const int64_t s = ent >> 5;
             const int b = (int)(ent & 31u);
-            const int64_t g = s * NB + b;
-            const float4 st = w.pv[g], a4 = w.na[g];
+            const int64_t g = (int64_t)b * n + s;
+            const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g];
             const int lastRail = meta_last_rail(w.meta[g]);
             const uint32_t restMask = w.restMask[s], dynMask = w.dynMask[s];
-            const v2 pos = mk(st.x, st.y), vel = mk(st.z, st.w), dn = mk(a4.x, a4.y);
+            const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y), dn = mk(q2n.x, q2n.y);
             dynPairMask = dynMask & ~((2u << b) - 1u);   // dynamic partners o > b (one job covers both orders)
             if (!is_zero(vel)) {
                 for (int r = 0; r < R; ++r) {
@@ -107,10 +112,10 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
                     if (!(disc < 0)) pocketMask |= 1u << k;
                 }
                 const float len1 = length(vel);
-                const float2* posOf = reinterpret_cast<const float2*>(w.pv + s * NB);
+                const float2* posOf = w.pos + s;
                 for (int o = 0; o < NB; ++o) {
                     if (!((restMask >> o) & 1u)) continue;
-                    const float2 q2 = posOf[2 * o];
+                    const float2 q2 = posOf[(int64_t)o * n];
                     const v2 toPoint = mk(q2.x, q2.y) - pos;
                     const float factor = dot(dn, toPoint) / len1;
                     const v2 dv = toPoint - (vel * factor);
@@ -119,10 +124,11 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
                 }
             }
         }
-        push_mask(railMask, ent << 5, qRails, &cnt.rails);
-        push_mask(pocketMask, ent << 5, qPockets, &cnt.pockets);
-        push_mask(statMask, ent << 6, qPairs, &cnt.pairs);
-        push_mask(dynPairMask, ent << 5, qDyn, &cnt.dynPairs);
+        sEnt[tid] = ent;
+        push_mask(railMask, (uint32_t)tid << 5, qRails, &cnt.rails);
+        push_mask(pocketMask, (uint32_t)tid << 5, qPockets, &cnt.pockets);
+        push_mask(statMask, (uint32_t)tid << 6, qPairs, &cnt.pairs);
+        push_mask(dynPairMask, (uint32_t)tid << 5, qDyn, &cnt.dynPairs);
         __syncthreads();
 
         // ---- stage 1b: moving-vs-moving pre-checks, one queued pair per thread ----------------------------------------
@@ -134,24 +140,24 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
                 uint32_t code = 0;
                 if (i < nd) {
                     const uint32_t c2 = qDyn[i];
-                    const uint32_t en = c2 >> 5;
+                    const uint32_t en = sEnt[c2 >> 5];
                     const int o = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5;
-                    const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
-                    const v2 p1 = mk(s1.x, s1.y), v1 = mk(s1.z, s1.w), p2 = mk(s2.x, s2.y), w2 = mk(s2.z, s2.w);
+                    const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
+                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], x2 = w.pos[g2], y2 = w.vel[g2];
+                    const v2 p1 = mk(x1.x, x1.y), v1 = mk(y1.x, y1.y), p2 = mk(x2.x, x2.y), w2 = mk(y2.x, y2.y);
                     // the reference tests b -> o and, on o's own turn, o -> b; the quantised coefficients of both
                     // orders are identical, so one job covers both
                     #pragma unroll 1
                     for (int turn = 0; turn < 2 && !pass; ++turn)   // one call site, operands swapped by select
                         pass = collision_precheck(turn ? w2 : v1, turn ? p2 : p1, turn ? v1 : w2, turn ? p1 : p2, diameter);
-                    code = (en << 6) | 32u | (uint32_t)o;
+                    code = ((c2 >> 5) << 6) | 32u | (uint32_t)o;
                 }
                 const unsigned m = __ballot_sync(FULL, pass);
                 if (m) {
                     int at = 0;
                     if (lane == 0) at = atomicAdd(&cnt.pairs, __popc(m));
                     at = __shfl_sync(FULL, at, 0);
-                    if (pass) qPairs[at + __popc(m & ((1u << lane) - 1u))] = code;
+                    if (pass) qPairs[at + __popc(m & ((1u << lane) - 1u))] = (uint16_t)code;
                 }
             }
         }
@@ -161,16 +167,18 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
         {
             const int cR = cnt.rails, cP = cnt.pockets, cQ = cnt.pairs;
             const int totalQ = cR + cP + cQ;
+            if (tid == 0 && cQ > 0) sJobBase = atomicAdd(jobCount, (uint32_t)cQ);   // one global atomic per tile
+            __syncthreads();
             for (int i0 = 0; i0 < totalQ; i0 += ITEM_BLOCK) {
                 const int i = i0 + tid;
                 const bool isRail = i < cR, isPocket = !isRail && i < cR + cP, isPair = !isRail && !isPocket && i < totalQ;
                 if (isRail) {
                     const uint32_t c2 = qRails[i];
-                    const uint32_t en = c2 >> 5;
+                    const uint32_t en = sEnt[c2 >> 5];
                     const int r = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5, g = s * NB + b;
-                    const float4 st = w.pv[g], a4 = w.na[g];
-                    const v2 pos = mk(st.x, st.y), vel = mk(st.z, st.w);
+                    const int64_t s = en >> 5, g = (int64_t)b * n + s;
+                    const float2 q0 = w.pos[g], q1 = w.vel[g], q3 = w.acc[g];
+                    const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y);
                     const RailGeom rg = sRails[r];
                     // lambda of halfLineIntersectsLineSegment, recomputed exactly as stage 1 did
                     const float detDV = vel.x * rg.dy - vel.y * rg.dx;
@@ -178,44 +186,36 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeW
                     const float lambda = (detVP + sDetQV[r]) / detDV;
                     const float distance = length(lambda * vel);
                     const float velocity = length(vel);
-                    const float a = -length(mk(a4.z, a4.w));
+                    const float a = -length(mk(q3.x, q3.y));
                     float x[2];
                     if (solve_quadratic(0.5f * a, velocity, -distance, x) != 0) offer(key + s, x[0], make_code(b, CAT_RAIL, r));
                 } else if (isPocket) {
                     const uint32_t c2 = qPockets[i - cR];
-                    const uint32_t en = c2 >> 5;
+                    const uint32_t en = sEnt[c2 >> 5];
                     const int k = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5, g = s * NB + b;
-                    const float4 st = w.pv[g], a4 = w.na[g];
+                    const int64_t s = en >> 5, g = (int64_t)b * n + s;
+                    const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g], q3 = w.acc[g];
                     float t;
-                    if (time_to_pocket(sPockets[k], mk(st.x, st.y), mk(a4.x, a4.y), mk(st.z, st.w), mk(a4.z, a4.w), &t))
+                    if (time_to_pocket(sPockets[k], mk(q0.x, q0.y), mk(q2n.x, q2n.y), mk(q1.x, q1.y), mk(q3.x, q3.y), &t))
                         offer(key + s, t, make_code(b, CAT_POCKET, k));
                 }
-                // pairs: quantised coefficients -> global job queue (one atomicAdd per warp)
-                const unsigned pm = __ballot_sync(FULL, isPair);
-                if (pm) {
-                    uint32_t jb = 0;
-                    const int leader = __ffs(pm) - 1;
-                    if (lane == leader) jb = atomicAdd(jobCount, (uint32_t)__popc(pm));
-                    jb = __shfl_sync(FULL, jb, leader);
-                    if (isPair) {
-                        const uint32_t c2 = qPairs[i - cR - cP];
-                        const uint32_t en = c2 >> 6;
-                        const int o = (int)(c2 & 31u), b = (int)(en & 31u);
-                        const int64_t s = en >> 5;
-                        const float4 s1 = w.pv[s * NB + b], s2 = w.pv[s * NB + o];
-                        const float4 a1 = w.na[s * NB + b], a2 = w.na[s * NB + o];
-                        float co[5];
-                        collision_coefficients(mk(a1.z, a1.w), mk(s1.z, s1.w), mk(s1.x, s1.y), mk(a2.z, a2.w), mk(s2.z, s2.w),
-                                               mk(s2.x, s2.y), diameter, co);
-                        const uint64_t j = (uint64_t)jb + __popc(pm & ((1u << lane) - 1u));
-                        if (j < w.jobCap) {
-                            #pragma unroll
-                            for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
-                            w.jobCode[j] = c2;
-                        } else {
-                            w.counts[4 * ROUNDS + 3] = 1u;  // queue overflow: the host grows the queue and re-runs the launch
-                        }
+                else if (isPair) {   // quantised coefficients -> global job queue
+                    const int iq = i - cR - cP;
+                    const uint32_t c2 = qPairs[iq];
+                    const uint32_t en = sEnt[c2 >> 6];
+                    const int o = (int)(c2 & 31u), b = (int)(en & 31u);
+                    const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
+                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2], y2 = w.vel[g2], z2 = w.acc[g2];
+                    float co[5];
+                    collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), mk(z2.x, z2.y), mk(y2.x, y2.y),
+                                           mk(x2.x, x2.y), diameter, co);
+                    const uint64_t j = (uint64_t)sJobBase + iq;
+                    if (j < w.jobCap) {
+                        #pragma unroll
+                        for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
+                        w.jobCode[j] = (en << 6) | (c2 & 63u);
+                    } else {
+                        w.counts[4 * ROUNDS + 3] = 1u;  // queue overflow: the host grows the queue and re-runs the launch
                     }
                 }
             }

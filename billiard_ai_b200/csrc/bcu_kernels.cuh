@@ -60,9 +60,11 @@ struct PipeWorkspace {
     void* base;
     int64_t n;                 // strikes this layout was made for
     size_t dynCap, jobCap;
-    // per ball [n][nBalls]
-    float4* pv;                // pos.xy, vel.xy
-    float4* na;                // velNormed.xy, acc.xy   (state::BallState, type.cpp:176-184)
+    // per ball, ball-major [nBalls][n]: threads of consecutive strikes touch consecutive words
+    float2* pos;
+    float2* vel;
+    float2* vn;                // velocityNormed (state::BallState, type.cpp:176-184)
+    float2* acc;
     float* nextRolling;        // < 0: none  (System::_nextRolling, type.cpp:478-527)
     uint32_t* meta;            // kind | rolling << 8 | (lastRail + 1) << 16 | (type + 1) << 24
     // per strike

@@ -98,15 +98,34 @@ __device__ __forceinline__ Candidate decode_candidate(const LaunchParams& p, int
     return c;
 }
 
-// Appends `pred` threads' values to a global list with one atomicAdd per warp.  Must be called by all 32 lanes.
-__device__ __forceinline__ void warp_append(bool pred, uint32_t value, uint32_t* list, uint32_t* counter) {
-    const unsigned m = __ballot_sync(0xffffffffu, pred);
-    if (m == 0) return;
-    const int lane = threadIdx.x & 31;
-    uint32_t base = 0;
-    if (lane == __ffs(m) - 1) base = atomicAdd(counter, (uint32_t)__popc(m));
-    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-    if (pred) list[base + __popc(m & ((1u << lane) - 1))] = value;
+// Reserves list slots for up to three predicates per thread with ONE global atomicAdd per predicate and CTA (same-address
+// atomics are the serial part of stream compaction).  All threads of the CTA must call; *slotK is valid where predK.
+struct AppendShared {
+    uint32_t warpCount[3][8];
+    uint32_t warpBase[3][8];
+};
+template <int NPRED>
+__device__ __forceinline__ void cta_reserve(AppendShared& sh, const bool (&pred)[NPRED], uint32_t* const (&counter)[NPRED],
+                                            uint32_t (&slot)[NPRED]) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nWarps = blockDim.x >> 5;
+    unsigned m[NPRED];
+    #pragma unroll
+    for (int k = 0; k < NPRED; ++k) {
+        m[k] = __ballot_sync(FULL, pred[k]);
+        if (lane == 0) sh.warpCount[k][warp] = __popc(m[k]);
+    }
+    __syncthreads();
+    if (threadIdx.x < NPRED) {
+        const int k = threadIdx.x;
+        uint32_t total = 0;
+        for (int i = 0; i < nWarps; ++i) { sh.warpBase[k][i] = total; total += sh.warpCount[k][i]; }
+        const uint32_t base = total ? atomicAdd(counter[k], total) : 0u;
+        for (int i = 0; i < nWarps; ++i) sh.warpBase[k][i] += base;
+    }
+    __syncthreads();
+    #pragma unroll
+    for (int k = 0; k < NPRED; ++k) slot[k] = sh.warpBase[k][warp] + __popc(m[k] & ((1u << lane) - 1u));
 }
 
 // A strike that reached its last layer is only MARKED here (flags | nEvents << 8, final layer time); the rules, the cost
@@ -117,61 +136,64 @@ __device__ __forceinline__ void mark_finished(const LaunchParams& p, int64_t s, 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// init: toInputLayer (billiard_search.cpp:760-795) + System::append of layer 0.  One warp per strike, lane = ball.
+// init: toInputLayer (billiard_search.cpp:760-795) + System::append of layer 0.  One thread per strike (the per-ball
+// arrays are ball-major, [ball][strike], so consecutive threads write consecutive words).
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) init_kernel(LaunchParams p, PipeWorkspace w) {
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
+    __shared__ AppendShared ash;
     const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
-    const int64_t warpsTotal = (int64_t)gridDim.x * (blockDim.x >> 5);
-    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
-        const Candidate c = decode_candidate(p, s);
-        int type = -1, kind = K_ABSENT;
-        v2 pos = mk(0.f, 0.f), vel = mk(0.f, 0.f), vn, acc;
-        float nextRolling = -1.0f;
-        if (lane < NB) {
-            type = p.states.type[(int64_t)c.sIdx * NB + lane];
-            if (type >= 0) {
-                const float2 q = reinterpret_cast<const float2*>(p.states.pos)[(int64_t)c.sIdx * NB + lane];
-                pos = mk(q.x, q.y);
-                if (type == p_rules.cueType) {
-                    vel = mk(c.vx, c.vy);
-                    kind = K_SHOT;
-                    nextRolling = time_to_rolling(vel, pc);  // type.cpp:502-506
-                } else {
-                    kind = K_REST;
+    const int64_t n = w.n;
+    for (int64_t base = (int64_t)blockIdx.x * 256; base < p.nCand; base += (int64_t)gridDim.x * 256) {
+        const int64_t s = base + threadIdx.x;
+        uint32_t dynMask = 0, restMask = 0;
+        if (s < p.nCand) {
+            const Candidate c = decode_candidate(p, s);
+            unsigned long long* key = w.key + s;  // buffer 0
+            for (int b = 0; b < NB; ++b) {
+                const int type = p.states.type[(int64_t)c.sIdx * NB + b];
+                int kind = K_ABSENT;
+                v2 pos = mk(0.f, 0.f), vel = mk(0.f, 0.f), vn, acc;
+                float nextRolling = -1.0f;
+                if (type >= 0) {
+                    const float2 q = reinterpret_cast<const float2*>(p.states.pos)[(int64_t)c.sIdx * NB + b];
+                    pos = mk(q.x, q.y);
+                    if (type == p_rules.cueType) {
+                        vel = mk(c.vx, c.vy);
+                        kind = K_SHOT;
+                        nextRolling = time_to_rolling(vel, pc);  // type.cpp:502-506
+                        dynMask |= 1u << b;
+                    } else {
+                        kind = K_REST;
+                        restMask |= 1u << b;
+                    }
+                }
+                derive_ball(vel, false, pc, &vn, &acc);
+                const int64_t g = (int64_t)b * n + s;
+                w.pos[g] = make_float2(pos.x, pos.y);
+                w.vel[g] = make_float2(vel.x, vel.y);
+                w.vn[g] = make_float2(vn.x, vn.y);
+                w.acc[g] = make_float2(acc.x, acc.y);
+                w.nextRolling[g] = nextRolling;
+                w.meta[g] = make_meta(kind, false, -1, type);
+                if (kind == K_SHOT) {
+                    offer(key, time_to_stop(acc, vel), make_code(b, CAT_REST, 0));
+                    if (nextRolling >= 0.0f) offer(key, nextRolling, make_code(b, CAT_ROLLING, 0));
                 }
             }
-        }
-        derive_ball(vel, false, pc, &vn, &acc);
-        if (lane < NB) {
-            const int64_t g = s * NB + lane;
-            w.pv[g] = make_float4(pos.x, pos.y, vel.x, vel.y);
-            w.na[g] = make_float4(vn.x, vn.y, acc.x, acc.y);
-            w.nextRolling[g] = nextRolling;
-            w.meta[g] = make_meta(kind, false, -1, type);
-        }
-        const unsigned dynMask = __ballot_sync(FULL, kind == K_SHOT);
-        const unsigned restMask = __ballot_sync(FULL, kind == K_REST);
-        if (kind == K_SHOT) {
-            unsigned long long* key = w.key + s;  // buffer 0
-            offer(key, time_to_stop(acc, vel), make_code(lane, CAT_REST, 0));
-            if (nextRolling >= 0.0f) offer(key, nextRolling, make_code(lane, CAT_ROLLING, 0));
-        }
-        if (lane == 0) {
             w.dynMask[s] = dynMask; w.restMask[s] = restMask; w.T[s] = 0.0f;
+            if (dynMask == 0) mark_finished(p, s, F_COMPLETED, 0, 0.0f);
         }
-        __syncwarp();
-        if (dynMask == 0) {
-            if (lane == 0) mark_finished(p, s, F_COMPLETED, 0, 0.0f);
-        } else {
-            if (lane == 0) w.live[atomicAdd(&w.counts[0], 1u)] = (uint32_t)s;
-            const int nd = __popc(dynMask);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&w.counts[1], (uint32_t)nd);
-            base = __shfl_sync(FULL, base, 0);
-            if (kind == K_SHOT) w.dyn[base + __popc(dynMask & ((1u << lane) - 1))] = ((uint32_t)s << 5) | lane;
+        // live strikes, and their dynamic balls (normally the one cue ball; further cue-type balls are appended one by one)
+        const bool pred[2] = {dynMask != 0, dynMask != 0};
+        uint32_t* const counter[2] = {&w.counts[0], &w.counts[1]};
+        uint32_t slot[2];
+        cta_reserve<2>(ash, pred, counter, slot);
+        if (dynMask != 0) {
+            w.live[slot[0]] = (uint32_t)s;
+            w.dyn[slot[1]] = ((uint32_t)s << 5) | (uint32_t)(__ffs(dynMask) - 1);
+            for (uint32_t m = dynMask & (dynMask - 1); m; m &= m - 1)
+                w.dyn[atomicAdd(&w.counts[1], 1u)] = ((uint32_t)s << 5) | (uint32_t)(__ffs(m) - 1);
         }
     }
 }
@@ -209,16 +231,18 @@ struct BallRec {
 };
 __device__ __forceinline__ BallRec load_ball(const PipeWorkspace& w, int64_t g) {
     BallRec r;
-    const float4 st = w.pv[g], a4 = w.na[g];
+    const float2 q0 = w.pos[g], q1 = w.vel[g], q2 = w.vn[g], q3 = w.acc[g];
     const uint32_t m = w.meta[g];
-    r.pos = mk(st.x, st.y); r.vel = mk(st.z, st.w); r.vn = mk(a4.x, a4.y); r.acc = mk(a4.z, a4.w);
+    r.pos = mk(q0.x, q0.y); r.vel = mk(q1.x, q1.y); r.vn = mk(q2.x, q2.y); r.acc = mk(q3.x, q3.y);
     r.nextRolling = w.nextRolling[g];
     r.kind = meta_kind(m); r.rolling = meta_rolling(m); r.lastRail = meta_last_rail(m); r.type = meta_type(m);
     return r;
 }
 __device__ __forceinline__ void store_ball(const PipeWorkspace& w, int64_t g, const BallRec& r) {
-    w.pv[g] = make_float4(r.pos.x, r.pos.y, r.vel.x, r.vel.y);
-    w.na[g] = make_float4(r.vn.x, r.vn.y, r.acc.x, r.acc.y);
+    w.pos[g] = make_float2(r.pos.x, r.pos.y);
+    w.vel[g] = make_float2(r.vel.x, r.vel.y);
+    w.vn[g] = make_float2(r.vn.x, r.vn.y);
+    w.acc[g] = make_float2(r.acc.x, r.acc.y);
     w.nextRolling[g] = r.nextRolling;
     w.meta[g] = make_meta(r.kind, r.rolling, r.lastRail, r.type);
 }
@@ -242,6 +266,7 @@ __device__ __forceinline__ void offer_own(unsigned long long* key, const BallRec
 }
 
 __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, PipeWorkspace w, int round) {
+    __shared__ AppendShared ash;
     const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
     const uint32_t nLive = w.counts[4 * round + 0], nDyn = w.counts[4 * round + 1];
@@ -287,7 +312,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                 const float deltaTime = newT - T;  // type.cpp:475
                 Tnext[s] = newT;
                 uint32_t dynMask = w.dynMask[s], restMask = w.restMask[s];
-                const int64_t gA = s * NB + evBall;
+                const int64_t gA = (int64_t)evBall * w.n + s;
                 BallRec A = load_ball(w, gA);
                 const v2 npos = advance_position(A.acc, A.vel, dt, A.pos);
                 const v2 nvel = advance_velocity(A.acc, A.vel, dt);
@@ -304,7 +329,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                 } else if (evType == E_ROLLING) {          // :1810-1840
                     A.vel = nvel; A.rolling = true; A.kind = K_MOVING;
                 } else {                                   // :1842-1905 createBallCollisionNodes
-                    const int64_t gB = s * NB + evPartner;
+                    const int64_t gB = (int64_t)evPartner * w.n + s;
                     BallRec B = load_ball(w, gB);
                     const v2 opos = advance_position(B.acc, B.vel, dt, B.pos);
                     const v2 ovel = advance_velocity(B.acc, B.vel, dt);
@@ -340,9 +365,15 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                 else appendLive = true;
             }
         }
-        warp_append(appendLive, sLive, liveNext, liveCountNext);
-        warp_append(appendA, entA, dynNext, dynCountNext);
-        warp_append(appendB, entB, dynNext, dynCountNext);
+        {
+            const bool pred[3] = {appendLive, appendA, appendB};
+            uint32_t* const counter[3] = {liveCountNext, dynCountNext, dynCountNext};
+            uint32_t slot[3];
+            cta_reserve<3>(ash, pred, counter, slot);
+            if (appendLive) liveNext[slot[0]] = sLive;
+            if (appendA) dynNext[slot[1]] = entA;
+            if (appendB) dynNext[slot[2]] = entB;
+        }
     }
 
     // ---- every other dynamic ball: closed-form advance to the new layer (createNodes :1907-1955) ---------------------
@@ -366,7 +397,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                     const float T = Tcur[s];
                     const float newT = T + dt;
                     const float deltaTime = newT - T;
-                    const int64_t g = s * NB + b;
+                    const int64_t g = (int64_t)b * w.n + s;
                     BallRec r = load_ball(w, g);
                     const v2 nv = advance_velocity(r.acc, r.vel, dt);
                     r.pos = advance_position(r.acc, r.vel, dt, r.pos);
@@ -379,7 +410,13 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
                 }
             }
         }
-        warp_append(keep, ent, dynNext, dynCountNext);
+        {
+            const bool pred[1] = {keep};
+            uint32_t* const counter[1] = {dynCountNext};
+            uint32_t slot[1];
+            cta_reserve<1>(ash, pred, counter, slot);
+            if (keep) dynNext[slot[0]] = ent;
+        }
     }
 }
 
@@ -395,11 +432,11 @@ __global__ void __launch_bounds__(256) finish_kernel(LaunchParams p, PipeWorkspa
         const Candidate c = decode_candidate(p, s);
         uint32_t flags = p.out.flags[s];
         int kind = K_ABSENT, type = -1;
-        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        float2 q = make_float2(0.f, 0.f);
         if (lane < NB) {
-            const uint32_t m = w.meta[s * NB + lane];
+            const uint32_t m = w.meta[(int64_t)lane * w.n + s];
             kind = meta_kind(m); type = meta_type(m);
-            q = w.pv[s * NB + lane];
+            q = w.pos[(int64_t)lane * w.n + s];
         }
         const unsigned pottedMask = __ballot_sync(FULL, kind == K_POTTING);
         const unsigned cuePotted = __ballot_sync(FULL, kind == K_POTTING && type == p_rules.cueType);
@@ -470,7 +507,8 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align(bytes); return o; };
     const size_t nb = (size_t)n * nBalls;
-    const size_t oPv = take(nb * sizeof(float4)), oNa = take(nb * sizeof(float4)), oNr = take(nb * sizeof(float));
+    const size_t oPos = take(nb * sizeof(float2)), oVel = take(nb * sizeof(float2)), oVn = take(nb * sizeof(float2));
+    const size_t oAcc = take(nb * sizeof(float2)), oNr = take(nb * sizeof(float));
     const size_t oMeta = take(nb * sizeof(uint32_t));
     const size_t oKey = take((size_t)3 * n * sizeof(unsigned long long));
     const size_t oT = take((size_t)2 * n * sizeof(float));
@@ -482,7 +520,8 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     if (layout) {
         unsigned char* b = reinterpret_cast<unsigned char*>(layout->base);
         w.base = layout->base;
-        w.pv = reinterpret_cast<float4*>(b + oPv); w.na = reinterpret_cast<float4*>(b + oNa);
+        w.pos = reinterpret_cast<float2*>(b + oPos); w.vel = reinterpret_cast<float2*>(b + oVel);
+        w.vn = reinterpret_cast<float2*>(b + oVn); w.acc = reinterpret_cast<float2*>(b + oAcc);
         w.nextRolling = reinterpret_cast<float*>(b + oNr); w.meta = reinterpret_cast<uint32_t*>(b + oMeta);
         w.key = reinterpret_cast<unsigned long long*>(b + oKey); w.T = reinterpret_cast<float*>(b + oT);
         w.dynMask = reinterpret_cast<uint32_t*>(b + oDm); w.restMask = reinterpret_cast<uint32_t*>(b + oRm);
@@ -503,7 +542,7 @@ cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& wsIn, in
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(w.counts, 0, (size_t)4 * (ROUNDS + 1) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
-    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * p.states.nBalls) * sizeof(uint32_t);
+    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * p.states.nBalls) * sizeof(uint16_t);
     static bool attrSet = false;
     if (!attrSet) {
         cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
