@@ -36,6 +36,14 @@ struct DevBuf {
 
 }  // namespace
 
+struct PipeGraphKey {   // everything the captured launch sequence depends on
+    void* ws; void* params; int64_t per; int G; int nBalls; int jobsPerStrike; bool counters;
+    bool operator==(const PipeGraphKey& o) const {
+        return ws == o.ws && params == o.params && per == o.per && G == o.G && nBalls == o.nBalls &&
+               jobsPerStrike == o.jobsPerStrike && counters == o.counters;
+    }
+};
+
 struct bcu_engine {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -71,7 +79,15 @@ struct bcu_engine {
     DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
     int sms = 148;
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
-    uint32_t* hOverflow = nullptr;   // pinned
+    uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
+    int pipeStreams = 4;             // BCU_STREAMS: parts of a launch in flight at once
+    cudaStream_t pipeStream[PIPE_MAX_STREAMS] = {};
+    cudaEvent_t pipeDone[PIPE_MAX_STREAMS] = {};
+    cudaEvent_t pipeFork = nullptr;
+    DevBuf<LaunchParams> dPipeParams;   // one parameter block per stream, read by the kernels
+    bool useGraph = true;               // BCU_NO_GRAPH / BCU_ROUND_TIMING: plain stream launches
+    cudaGraphExec_t pipeGraph = nullptr;
+    PipeGraphKey pipeKey{};
     int kernelVersion = 3;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
     // top-k
     DevBuf<unsigned char> dTopkScratch;
@@ -222,6 +238,11 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     e->maxCtas = simulate_max_ctas(device);
     cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
     if (const char* kv = getenv("BCU_KERNEL")) e->kernelVersion = atoi(kv) == 2 ? 2 : 3;
+    if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
+    if (const char* sv = getenv("BCU_STREAMS")) {
+        const int v = atoi(sv);
+        e->pipeStreams = v < 1 ? 1 : v > PIPE_MAX_STREAMS ? PIPE_MAX_STREAMS : v;
+    }
     if (cudaGetLastError() != cudaSuccess) { delete e; return BCU_ERR_CUDA; }
     *out = e;
     return BCU_OK;
@@ -241,6 +262,13 @@ void bcu_destroy(bcu_engine* e) {
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
     if (e->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->ncclComm);
     if (e->hOverflow) cudaFreeHost(e->hOverflow);
+    for (int g = 0; g < PIPE_MAX_STREAMS; ++g) {
+        if (e->pipeDone[g]) cudaEventDestroy(e->pipeDone[g]);
+        if (e->pipeStream[g]) cudaStreamDestroy(e->pipeStream[g]);
+    }
+    if (e->pipeFork) cudaEventDestroy(e->pipeFork);
+    if (e->pipeGraph) cudaGraphExecDestroy(e->pipeGraph);
+    e->dPipeParams.release();
     if (e->evT0) cudaEventDestroy(e->evT0);
     if (e->evT1) cudaEventDestroy(e->evT1);
     if (e->evStart) cudaEventDestroy(e->evStart);
@@ -317,31 +345,83 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
         CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
         e->launches++;
     } else {
-        // batch path: chunks of at most PIPE_MAX_STRIKES strikes through the event-synchronous pipeline
-        const int64_t chunk = p.nCand < PIPE_MAX_STRIKES ? p.nCand : PIPE_MAX_STRIKES;
-        if (!e->hOverflow) CK(cudaMallocHost(&e->hOverflow, sizeof(uint32_t)));
-        for (int64_t off = 0; off < p.nCand; off += chunk) {
-            LaunchParams q = p;
-            q.nCand = p.nCand - off < chunk ? p.nCand - off : chunk;
-            if (q.src.gridDirs > 0) {
-                q.src.firstCandidate += off;
-            } else {
-                q.src.stateIdx += off; q.src.vx += off; q.src.vy += off; q.src.searchCost += off; q.src.baseCost += off;
+        // batch path: the event-synchronous pipeline.  A launch is cut into parts that run on separate streams: every
+        // part is a chain of ~100 short kernels whose rounds are latency-bound, so independent parts fill each other's
+        // gaps (a part is still large enough to keep the stream-compacted kernels dense).  The whole fork / chains / join
+        // sequence is captured once into a CUDA graph (kernel parameters live in device memory, grids are persistent),
+        // so a level costs one graph launch instead of several hundred kernel launches.
+        const int nBalls = p.states.nBalls;
+        int64_t per = (p.nCand + e->pipeStreams - 1) / e->pipeStreams;
+        if (per < 8192) per = 8192;
+        if (per > PIPE_MAX_STRIKES) per = PIPE_MAX_STRIKES;
+        per = (per + 255) & ~(int64_t)255;
+        const int64_t nParts = (p.nCand + per - 1) / per;
+        const int G = (int)(nParts < e->pipeStreams ? nParts : e->pipeStreams);
+        const bool withCounters = p.out.counters != nullptr;
+        if (!e->hOverflow) CK(cudaMallocHost(&e->hOverflow, PIPE_MAX_STREAMS * sizeof(uint32_t)));
+        for (int g = 0; g < G; ++g) {
+            if (!e->pipeStream[g]) {
+                CK(cudaStreamCreateWithFlags(&e->pipeStream[g], cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&e->pipeDone[g], cudaEventDisableTiming));
             }
-            q.out.cost += off; q.out.flags += off; q.out.potted += off; q.out.finalTime += off;
-            if (q.out.finalPos) q.out.finalPos += (size_t)off * p.states.nBalls * 2;
-            if (q.out.eventLog) q.out.eventLog += (size_t)off * 32;
+        }
+        if (!e->pipeFork) CK(cudaEventCreateWithFlags(&e->pipeFork, cudaEventDisableTiming));
+        CK(e->dPipeParams.reserve(PIPE_MAX_STREAMS));
+        for (int64_t wave = 0; wave < nParts; wave += G) {
             for (;;) {
-                PipeWorkspace ws{};
-                CK(e->dPipeWs.reserve(pipeline_workspace_bytes(chunk, p.states.nBalls, e->jobsPerStrike, nullptr)));
-                ws.base = e->dPipeWs.p;
-                pipeline_workspace_bytes(chunk, p.states.nBalls, e->jobsPerStrike, &ws);
-                CK(launch_pipeline(q, ws, e->sms, e->stream));
-                e->launches += pipeline_launch_count();
-                // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
-                CK(cudaMemcpyAsync(e->hOverflow, pipeline_overflow_flag(ws), sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+                const size_t wsBytes = pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, nullptr);
+                CK(e->dPipeWs.reserve(wsBytes * G));
+                // this wave's parameter blocks
+                LaunchParams hp[PIPE_MAX_STREAMS];
+                for (int g = 0; g < G; ++g) {
+                    const int64_t off = (wave + g) * per;
+                    LaunchParams q = p;
+                    q.nCand = off >= p.nCand ? 0 : (p.nCand - off < per ? p.nCand - off : per);
+                    if (q.nCand > 0) {
+                        if (q.src.gridDirs > 0) {
+                            q.src.firstCandidate += off;
+                        } else {
+                            q.src.stateIdx += off; q.src.vx += off; q.src.vy += off; q.src.searchCost += off; q.src.baseCost += off;
+                        }
+                        q.out.cost += off; q.out.flags += off; q.out.potted += off; q.out.finalTime += off;
+                        if (q.out.finalPos) q.out.finalPos += (size_t)off * nBalls * 2;
+                        if (q.out.eventLog) q.out.eventLog += (size_t)off * 32;
+                    }
+                    hp[g] = q;
+                }
+                CK(cudaMemcpyAsync(e->dPipeParams.p, hp, G * sizeof(LaunchParams), cudaMemcpyHostToDevice, e->stream));
+                PipeGraphKey key{e->dPipeWs.p, e->dPipeParams.p, per, G, nBalls, e->jobsPerStrike, withCounters};
+                const bool useGraph = e->useGraph;
+                if (!useGraph || !e->pipeGraph || !(key == e->pipeKey)) {
+                    if (e->pipeGraph) { cudaGraphExecDestroy(e->pipeGraph); e->pipeGraph = nullptr; }
+                    if (useGraph) CK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+                    CK(cudaEventRecord(e->pipeFork, e->stream));
+                    for (int g = 0; g < G; ++g) {
+                        PipeWorkspace ws{};
+                        ws.base = e->dPipeWs.p + wsBytes * g;
+                        pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, &ws);
+                        CK(cudaStreamWaitEvent(e->pipeStream[g], e->pipeFork, 0));
+                        CK(launch_pipeline(e->dPipeParams.p + g, nBalls, withCounters, ws, e->sms, e->pipeStream[g], true));
+                        // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
+                        CK(cudaMemcpyAsync(e->hOverflow + g, pipeline_overflow_flag(ws), sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                           e->pipeStream[g]));
+                        CK(cudaEventRecord(e->pipeDone[g], e->pipeStream[g]));
+                        CK(cudaStreamWaitEvent(e->stream, e->pipeDone[g], 0));
+                    }
+                    if (useGraph) {
+                        cudaGraph_t graph = nullptr;
+                        CK(cudaStreamEndCapture(e->stream, &graph));
+                        CK(cudaGraphInstantiate(&e->pipeGraph, graph, 0));
+                        cudaGraphDestroy(graph);
+                        e->pipeKey = key;
+                    }
+                }
+                if (useGraph) CK(cudaGraphLaunch(e->pipeGraph, e->stream));
+                e->launches += (int64_t)G * pipeline_launch_count();
                 CK(cudaStreamSynchronize(e->stream));
-                if (*e->hOverflow == 0) break;
+                bool overflow = false;
+                for (int g = 0; g < G; ++g) overflow |= e->hOverflow[g] != 0;
+                if (!overflow) break;
                 if (e->jobsPerStrike >= 1024) return fail(e, BCU_ERR_STATE, "quartic job queue overflow");
                 e->jobsPerStrike *= 2;
             }

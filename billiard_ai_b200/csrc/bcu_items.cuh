@@ -44,7 +44,8 @@ __device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint16_t
     }
 }
 
-__global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(LaunchParams p, PipeWorkspace w, int round) {
+__global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    const LaunchParams& p = *pp;
     extern __shared__ uint16_t smemQ[];
     __shared__ ItemCounts cnt;
     __shared__ uint32_t sEnt[ITEM_BLOCK];

@@ -54,6 +54,7 @@ struct LaunchParams {
 
 // ---- K1 v3, the event-synchronous batch pipeline (bcu_pipeline.cu) ----------------------------------------------
 constexpr int64_t PIPE_MAX_STRIKES = 1 << 20;   // per launch; larger batches are chunked by the caller
+constexpr int PIPE_MAX_STREAMS = 8;
 constexpr int PIPE_JOBS_PER_STRIKE = 8;          // initial quartic-queue capacity per strike and round; on overflow the
                                                  // launch raises a flag and the host doubles the queue and re-runs it
 struct PipeWorkspace {
@@ -83,7 +84,8 @@ struct PipeWorkspace {
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
 void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
-cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& w, int sms, cudaStream_t stream);
+cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, bool withCounters, const PipeWorkspace& w, int sms,
+                            cudaStream_t stream, bool resetOverflow);
 int pipeline_launch_count();
 
 void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);

@@ -26,6 +26,10 @@
 // kernel reads a word another thread of the same launch writes.
 #include <cuda_runtime.h>
 
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
 #include "bcu_kernels.cuh"
 #include "bcu_physics.cuh"
 
@@ -139,7 +143,8 @@ __device__ __forceinline__ void mark_finished(const LaunchParams& p, int64_t s, 
 // init: toInputLayer (billiard_search.cpp:760-795) + System::append of layer 0.  One thread per strike (the per-ball
 // arrays are ball-major, [ball][strike], so consecutive threads write consecutive words).
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) init_kernel(LaunchParams p, PipeWorkspace w) {
+__global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    const LaunchParams& p = *pp;
     __shared__ AppendShared ash;
     const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
@@ -265,7 +270,8 @@ __device__ __forceinline__ void offer_own(unsigned long long* key, const BallRec
     if (r.nextRolling >= 0.0f) offer(key, r.nextRolling, make_code(b, CAT_ROLLING, 0));
 }
 
-__global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, PipeWorkspace w, int round) {
+__global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    const LaunchParams& p = *pp;
     __shared__ AppendShared ash;
     const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
@@ -422,7 +428,8 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(LaunchParams p, Pipe
 
 // rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
 // One warp per strike, lane = ball.
-__global__ void __launch_bounds__(256) finish_kernel(LaunchParams p, PipeWorkspace w) {
+__global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    const LaunchParams& p = *pp;
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int NB = p.states.nBalls;
@@ -471,7 +478,8 @@ __global__ void __launch_bounds__(256) finish_kernel(LaunchParams p, PipeWorkspa
 }
 
 // work counters from the per-round list sizes: [1] pair items [2] quartics [3] rail items [4] pocket items
-__global__ void counters_kernel(LaunchParams p, PipeWorkspace w) {
+__global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    const LaunchParams& p = *pp;
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long pairs = 0, quartics = 0, rails = 0, pockets = 0;
     for (int r = 0; r < ROUNDS; ++r) {
@@ -480,7 +488,8 @@ __global__ void counters_kernel(LaunchParams p, PipeWorkspace w) {
         pairs += d * p.states.nBalls; rails += d * p_table.nRails; pockets += d * p_table.nPockets;
         quartics += w.counts[4 * r + 2];
     }
-    p.out.counters[1] += pairs; p.out.counters[2] += quartics; p.out.counters[3] += rails; p.out.counters[4] += pockets;
+    atomicAdd(&p.out.counters[1], pairs); atomicAdd(&p.out.counters[2], quartics);
+    atomicAdd(&p.out.counters[3], rails); atomicAdd(&p.out.counters[4], pockets);
 }
 
 }  // namespace
@@ -490,6 +499,8 @@ static int g_nRails = MAX_RAILS, g_nPockets = MAX_POCKETS;
 void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream) {
     PhysConst pc = phys_const();
     g_nRails = table.nRails; g_nPockets = table.nPockets;
+    cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(ITEM_BLOCK * (MAX_RAILS + MAX_POCKETS + 2 * MAX_BALLS) * sizeof(uint16_t)));
     cudaMemcpyToSymbolAsync(p_table, &table, sizeof(TableGeom), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(p_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
@@ -535,29 +546,57 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
 
 int pipeline_launch_count() { return 2 + 3 * ROUNDS; }
 
-// One launch of the batch path over p.nCand <= PIPE_MAX_STRIKES strikes.  `w` must have been laid out for >= p.nCand.
-cudaError_t launch_pipeline(const LaunchParams& p, const PipeWorkspace& wsIn, int sms, cudaStream_t stream) {
-    if (p.nCand <= 0) return cudaSuccess;
+// One launch of the batch path over p->nCand <= w.n strikes.  `p` is a DEVICE pointer (the kernels read their parameters
+// from memory, so a captured CUDA graph of this sequence stays valid from call to call); all grids are persistent and
+// sized by the workspace capacity, so nothing in the launch sequence depends on the candidate count.
+cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, bool withCounters, const PipeWorkspace& wsIn, int sms,
+                            cudaStream_t stream, bool resetOverflow) {
     PipeWorkspace w = wsIn;
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(w.counts, 0, (size_t)4 * (ROUNDS + 1) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
-    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * p.states.nBalls) * sizeof(uint16_t);
-    static bool attrSet = false;
-    if (!attrSet) {
-        cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(ITEM_BLOCK * (MAX_RAILS + MAX_POCKETS + 2 * MAX_BALLS) * sizeof(uint32_t)));
-        attrSet = true;
-    }
-    const int64_t initBlocks = (p.nCand + 7) / 8;
+    // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
+    const size_t countWords = (size_t)4 * (ROUNDS + 1) - (resetOverflow ? 0 : 1);
+    if ((e = cudaMemsetAsync(w.counts, 0, countWords * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * nBalls) * sizeof(uint16_t);
+    const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
+    // BCU_ROUND_TIMING=1 (diagnosis only): CUDA events around every kernel, per-round times on stderr
+    static const bool timing = getenv("BCU_ROUND_TIMING") != nullptr;
+    std::vector<cudaEvent_t> ev;
+    auto mark = [&]() {
+        if (!timing) return;
+        cudaEvent_t x; cudaEventCreate(&x); cudaEventRecord(x, stream); ev.push_back(x);
+    };
+    mark();
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
+    mark();
     for (int r = 0; r < ROUNDS; ++r) {
         items_kernel<<<sms * 8, ITEM_BLOCK, itemSmem, stream>>>(p, w, r);
+        mark();
         quartic_kernel<<<sms * 4, QUARTIC_BLOCK, 0, stream>>>(w, r);
+        mark();
         apply_kernel<<<sms * 4, APPLY_BLOCK, 0, stream>>>(p, w, r);
+        mark();
     }
-    finish_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
-    if (p.out.counters) counters_kernel<<<1, 32, 0, stream>>>(p, w);
+    finish_kernel<<<(unsigned)(finBlocks < sms * 8 ? finBlocks : sms * 8), 256, 0, stream>>>(p, w);
+    mark();
+    if (timing) {
+        cudaStreamSynchronize(stream);
+        std::vector<uint32_t> counts(4 * (ROUNDS + 1));
+        cudaMemcpy(counts.data(), w.counts, counts.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+        auto ms = [&](size_t i) { float t = 0; cudaEventElapsedTime(&t, ev[i], ev[i + 1]); return t * 1000.0f; };
+        float sum[3] = {0, 0, 0};
+        fprintf(stderr, "[bcu timing] init %.1f us\n", ms(0));
+        for (int r = 0; r < ROUNDS; ++r) {
+            fprintf(stderr, "[bcu timing] round %2d live %7u dyn %7u jobs %7u : items %6.1f quartic %6.1f apply %6.1f us\n", r,
+                    counts[4 * r], counts[4 * r + 1], counts[4 * r + 2], ms(1 + 3 * r), ms(2 + 3 * r), ms(3 + 3 * r));
+            for (int k = 0; k < 3; ++k) sum[k] += ms(1 + 3 * r + k);
+        }
+        float tot = 0; cudaEventElapsedTime(&tot, ev.front(), ev.back());
+        fprintf(stderr, "[bcu timing] finish %.1f us; items %.0f quartic %.0f apply %.0f; total %.0f us\n", ms(ev.size() - 2), sum[0],
+                sum[1], sum[2], tot * 1000.0f);
+        for (auto x : ev) cudaEventDestroy(x);
+    }
+    if (withCounters) counters_kernel<<<1, 32, 0, stream>>>(p, w);
     return cudaGetLastError();
 }
 
