@@ -386,97 +386,74 @@ BCU_HD void g_sincos(double x, double* sinx, double* cosx) {
     const uint32_t k = (uint32_t)(d2u(x) >> 32) & 0x7fffffff;
     const double ax = fabs(x);
     if (k < 0x3e400000) { *sinx = x; *cosx = 1.0; return; }  // |x| < 2^-27
-    if (k < 0x3feb6000) {                                    // |x| < 0.855469: do_sin(x,0), do_cos(x,0)
-        const double u = ax + big;
+    if (k < 0x3ff70a3d) {
+        // |x| < 0.855469:          sin = do_sin(x, 0) (Taylor below 0.126),  cos = do_cos(x, 0)
+        // 0.855469 <= |x| < 1.44:  a + da = pi/2 - |x|;  sin = copysign(do_cos(a, da), x),  cos = do_sin(a, da)
+        // (glibc's second range ends at 2.426265; the arguments of this path stay below pi/3.)
+        // do_sin / do_cos are the same two instruction streams in both ranges, so they are evaluated once on the selected
+        // table argument and the results are routed by selects -- the lanes of a warp fall into both ranges.
+        const bool hiRange = k >= 0x3feb6000;
+        const double y = hp0 - ax;
+        const double a = y + hp1;
+        const double da = (y - a) + hp1;
+        const double A = hiRange ? fabs(a) : ax;
+        const double u = A + big;
         const uint32_t j = ((uint32_t)d2u(u)) << 2;
-        const double xr = ax - (u - big);
-        SinCosTab T;
-        T.sn = BCU_TABD(BCU_SINCOS_TAB, j); T.ssn = BCU_TABD(BCU_SINCOS_TAB, j + 1);
-        T.cs = BCU_TABD(BCU_SINCOS_TAB, j + 2); T.ccs = BCU_TABD(BCU_SINCOS_TAB, j + 3);
-        if (ax < 0.126) {
-            // TAYLOR_SIN (xx, x, 0)
-            const double s1 = -0.16666666666666666, s2 = 0.008333333333332329, s3 = -0.00019841269834414642;
-            const double s4 = 2.755729806860771e-06, s5 = -2.5022014848318398e-08;
-            const double xx = x * x;
-            double p = bcu_fma(s5, xx, s4);
-            p = bcu_fma(p, xx, s3);
-            p = bcu_fma(p, xx, s2);
-            p = bcu_fma(p, xx, s1);
-            const double t1 = bcu_fma(p, x, -0.0);
-            const double t = bcu_fma(xx, t1, 0.0);
-            *sinx = x + t;
-        } else {
-            const double dx = (x > 0) ? 0.0 : -0.0;
+        const double xr = A - (u - big);
+        const double sn = BCU_TABD(BCU_SINCOS_TAB, j), ssn = BCU_TABD(BCU_SINCOS_TAB, j + 1);
+        const double cs = BCU_TABD(BCU_SINCOS_TAB, j + 2), ccs = BCU_TABD(BCU_SINCOS_TAB, j + 3);
+        double S, C;
+        {   // do_sin (xr, dxs)
+            const double dxs = hiRange ? ((a <= 0) ? -da : da) : ((x > 0) ? 0.0 : -0.0);
             const double xx = xr * xr;
             const double x3 = xx * xr;
             const double ps = bcu_fma(xx, sn5, sn3);
-            double s = bcu_fma(x3, ps, dx);
+            double s1 = bcu_fma(x3, ps, dxs);
             double pc = bcu_fma(xx, cs6, cs4);
-            s = s + xr;
+            s1 = s1 + xr;
             pc = bcu_fma(pc, xx, cs2);
             double c = xx * pc;
-            c = bcu_fma(dx, xr, c);
-            double cor = bcu_fma(s, T.ccs, T.ssn);
-            cor = bcu_fma(-c, T.sn, cor);
-            cor = bcu_fma(s, T.cs, cor);
-            *sinx = copysign(cor + T.sn, x);
+            c = bcu_fma(dxs, xr, c);
+            double cor = bcu_fma(s1, ccs, ssn);
+            cor = bcu_fma(-c, sn, cor);
+            cor = bcu_fma(s1, cs, cor);
+            S = cor + sn;
         }
-        {
-            const double dxc = (x < 0) ? -0.0 : 0.0;
+        {   // do_cos (xr + dxc)
+            const double dxc = hiRange ? da : ((x < 0) ? -0.0 : 0.0);
             const double xc = dxc + xr;
             const double xx = xc * xc;
             const double x3 = xc * xx;
             const double ps = bcu_fma(xx, sn5, sn3);
             double pc = bcu_fma(xx, cs6, cs4);
-            const double s = bcu_fma(x3, ps, xc);
+            const double s1 = bcu_fma(x3, ps, xc);
             pc = bcu_fma(pc, xx, cs2);
-            double cor = bcu_fma(-T.ssn, s, T.ccs);
+            double cor = bcu_fma(-ssn, s1, ccs);
             const double c = xx * pc;
-            cor = bcu_fma(-c, T.cs, cor);
-            cor = bcu_fma(-s, T.sn, cor);
-            *cosx = cor + T.cs;
+            cor = bcu_fma(-c, cs, cor);
+            cor = bcu_fma(-s1, sn, cor);
+            C = cor + cs;
         }
-        return;
-    }
-    if (k < 0x3ff70a3d) {                                    // 0.855469 <= |x| < 1.44 (glibc: < 2.426265, a > 0.126 here)
-        const double y = hp0 - ax;
-        const double a = y + hp1;
-        const double da = (y - a) + hp1;
-        const double aa = fabs(a);
-        const double u = aa + big;
-        const uint32_t j = ((uint32_t)d2u(u)) << 2;
-        const double xr = aa - (u - big);
-        const double sn = BCU_TABD(BCU_SINCOS_TAB, j), ssn = BCU_TABD(BCU_SINCOS_TAB, j + 1);
-        const double cs = BCU_TABD(BCU_SINCOS_TAB, j + 2), ccs = BCU_TABD(BCU_SINCOS_TAB, j + 3);
-        {   // *sinx = copysign(do_cos(a, da), x)
-            const double xc = xr + da;
-            const double xx = xc * xc;
-            const double x3 = xc * xx;
-            const double ps = bcu_fma(xx, sn5, sn3);
-            const double s = bcu_fma(x3, ps, xc);
-            double pc = bcu_fma(xx, cs6, cs4);
-            pc = bcu_fma(pc, xx, cs2);
-            const double c = xx * pc;
-            double cor = bcu_fma(-s, ssn, ccs);
-            cor = bcu_fma(-cs, c, cor);
-            cor = bcu_fma(-s, sn, cor);
-            *sinx = copysign(cs + cor, x);
-        }
-        {   // *cosx = do_sin(a, da)
-            const double dx = (a <= 0) ? -da : da;
-            const double xx = xr * xr;
-            double pc = bcu_fma(xx, cs6, cs4);
-            const double ps = bcu_fma(xx, sn5, sn3);
-            const double x3 = xx * xr;
-            pc = bcu_fma(pc, xx, cs2);
-            double s = bcu_fma(x3, ps, dx);
-            pc = xx * pc;
-            s = s + xr;
-            const double c = bcu_fma(dx, xr, pc);
-            double cor = bcu_fma(ccs, s, ssn);
-            cor = bcu_fma(-c, sn, cor);
-            cor = bcu_fma(s, cs, cor);
-            *cosx = copysign(cor + sn, a);
+        if (hiRange) {
+            *sinx = copysign(C, x);
+            *cosx = copysign(S, a);
+        } else {
+            *cosx = C;
+            if (ax < 0.126) {
+                // TAYLOR_SIN (xx, x, 0)
+                const double s1 = -0.16666666666666666, s2 = 0.008333333333332329, s3 = -0.00019841269834414642;
+                const double s4 = 2.755729806860771e-06, s5 = -2.5022014848318398e-08;
+                const double xx = x * x;
+                double p = bcu_fma(s5, xx, s4);
+                p = bcu_fma(p, xx, s3);
+                p = bcu_fma(p, xx, s2);
+                p = bcu_fma(p, xx, s1);
+                const double t1 = bcu_fma(p, x, -0.0);
+                const double t = bcu_fma(xx, t1, 0.0);
+                *sinx = x + t;
+            } else {
+                *sinx = copysign(S, x);
+            }
         }
         return;
     }
@@ -516,115 +493,67 @@ BCU_HD double g_atan2(double y, double x) {
     }
     if (ax < twom500 || ay < twom500) { ax = ax * two500; ay = ay * two500; }
     if (ax > two500 || ay > two500) { ax = ax * twom500; ay = ay * twom500; }
-    double u, du;
-    if (ay < ax) {
-        u = ay / ax;
-        const double v = u * ax;
-        const double vv = bcu_fma(u, ax, -v);
-        du = ((ay - v) - vv) / ax;
-    } else {
-        u = ax / ay;
-        const double v = u * ay;
-        const double vv = bcu_fma(u, ay, -v);
-        du = ((ax - v) - vv) / ay;
-    }
+    // u = min/max, du = its correction: one stream for both orders (operands selected)
+    const bool yLess = ay < ax;
+    const double num = yLess ? ay : ax, den = yLess ? ax : ay;
+    const double u = num / den;
+    const double du = ((num - u * den) - bcu_fma(u, den, -(u * den))) / den;
     double z;
-    if (x > 0) {
-        if (ay < ax) {                                    // (i) atan(ay/ax)
-            if (u < inv16) {
-                const double v = u * u;
-                const double p = atan2_poly(v);
-                const double zz = bcu_fma(u * v, p, du);
-                z = u + zz;
-            } else {
-                const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
-                const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), t1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
-                const double t2 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2), c3 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3);
-                const double c4 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4), c5 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5);
-                const double c6 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6);
-                const double t3 = u - c0;
-                const double v = du + t3;                 // EADD (t3, du, v, dv)
-                const double dv = (fabs(t3) > fabs(du)) ? ((t3 - v) + du) : ((du - v) + t3);
-                const double vsq = v * v;
-                double q = bcu_fma(c6, v, c5);
-                q = bcu_fma(q, v, c4);
-                q = bcu_fma(q, v, c3);
-                q = vsq * q;
-                q = bcu_fma(dv, t2, q);
-                const double zz = bcu_fma(v, t2, q);
-                z = zz + t1;
-            }
-        } else {                                          // (ii) pi/2 - atan(ax/ay)
-            if (u < inv16) {
-                const double v = u * u;
-                const double p = atan2_poly(v);
-                const double zz = (u * v) * p;
-                const double t2 = hpi - u;                // ESUB (hpi, u, t2, cor)
-                const double cor = (hpi > fabs(u)) ? ((hpi - t2) - u) : (hpi - (u + t2));
-                double t3 = cor + hpi1;
-                t3 = t3 - du;
-                t3 = t3 - zz;
-                z = t3 + t2;
-            } else {
-                const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
-                const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), c1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
-                const double v = (u - c0) + du;
-                double q = bcu_fma(BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6), v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2));
-                const double zz = bcu_fma(-q, v, hpi1);
-                const double t1 = hpi - c1;
-                z = t1 + zz;
-            }
+    if (x > 0 && yLess) {                                 // (i) atan(ay/ax)
+        if (u < inv16) {
+            const double v = u * u;
+            const double p = atan2_poly(v);
+            const double zz = bcu_fma(u * v, p, du);
+            z = u + zz;
+        } else {
+            const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
+            const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), t1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
+            const double t2 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2), c3 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3);
+            const double c4 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4), c5 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5);
+            const double c6 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6);
+            const double t3 = u - c0;
+            const double v = du + t3;                 // EADD (t3, du, v, dv)
+            const double dv = (fabs(t3) > fabs(du)) ? ((t3 - v) + du) : ((du - v) + t3);
+            const double vsq = v * v;
+            double q = bcu_fma(c6, v, c5);
+            q = bcu_fma(q, v, c4);
+            q = bcu_fma(q, v, c3);
+            q = vsq * q;
+            q = bcu_fma(dv, t2, q);
+            const double zz = bcu_fma(v, t2, q);
+            z = zz + t1;
         }
     } else {
-        if (ay > ax) {                                    // (iii) pi/2 + atan(ax/ay)
-            if (u < inv16) {
-                const double v = u * u;
-                const double p = atan2_poly(v);
-                const double zz = (u * v) * p;
-                const double t2 = u + hpi;                // EADD (hpi, u, t2, cor)
-                const double cor = (hpi > fabs(u)) ? ((hpi - t2) + u) : ((u - t2) + hpi);
-                double t3 = cor + hpi1;
-                t3 = t3 + du;
-                t3 = t3 + zz;
-                z = t3 + t2;
-            } else {
-                const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
-                const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), c1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
-                const double v = (u - c0) + du;
-                const double t1 = hpi + c1;
-                double q = bcu_fma(BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6), v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2));
-                const double zz = bcu_fma(q, v, hpi1);
-                z = t1 + zz;
-            }
-        } else {                                          // (iv) pi - atan(ay/ax)
-            if (u < inv16) {
-                const double v = u * u;
-                const double p = atan2_poly(v);
-                const double zz = (u * v) * p;
-                const double t2 = opi - u;                // ESUB (opi, u, t2, cor)
-                const double cor = (opi > fabs(u)) ? ((opi - t2) - u) : (opi - (u + t2));
-                double t3 = cor + opi1;
-                t3 = t3 - du;
-                t3 = t3 - zz;
-                z = t3 + t2;
-            } else {
-                const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
-                const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), c1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
-                const double v = (u - c0) + du;
-                double q = bcu_fma(BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6), v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3));
-                q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2));
-                const double zz = bcu_fma(-q, v, opi1);
-                const double t1 = opi - c1;
-                z = t1 + zz;
-            }
+        // (ii) x > 0, ay >= ax:  pi/2 - atan(ax/ay)      base = pi/2, sign -
+        // (iii) x < 0, ay > ax:  pi/2 + atan(ax/ay)      base = pi/2, sign +
+        // (iv) x < 0, ay <= ax:  pi   - atan(ay/ax)      base = pi,   sign -
+        // glibc writes the three with explicit + / -; a - b == a + (-b) and fma(-q, v, c) == fma(q, -v, c) bit for bit,
+        // so one stream with a sign serves all three.
+        const bool plus = !(x > 0) && ay > ax;
+        const bool usePi = !(x > 0) && !(ay > ax);
+        const double base = usePi ? opi : hpi, base1 = usePi ? opi1 : hpi1;
+        if (u < inv16) {
+            const double v = u * u;
+            const double p = atan2_poly(v);
+            const double zz = (u * v) * p;
+            const double su = plus ? u : -u, sdu = plus ? du : -du, szz = plus ? zz : -zz;
+            const double t2 = base + su;              // ESUB / EADD (base, u, t2, cor); base > |u| here (u < 1/16)
+            const double cor = (base - t2) + su;
+            double t3 = cor + base1;
+            t3 = t3 + sdu;
+            t3 = t3 + szz;
+            z = t3 + t2;
+        } else {
+            const int i = (int)(bcu_fma(u, two8, two52) - two52) - 16;
+            const double c0 = BCU_TABD(BCU_ATAN_CIJ, 7 * i), c1 = BCU_TABD(BCU_ATAN_CIJ, 7 * i + 1);
+            const double v = (u - c0) + du;
+            double q = bcu_fma(BCU_TABD(BCU_ATAN_CIJ, 7 * i + 6), v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 5));
+            q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 4));
+            q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 3));
+            q = bcu_fma(q, v, BCU_TABD(BCU_ATAN_CIJ, 7 * i + 2));
+            const double zz = bcu_fma(plus ? q : -q, v, base1);
+            const double t1 = base + (plus ? c1 : -c1);
+            z = t1 + zz;
         }
     }
     return copysign(z, y);

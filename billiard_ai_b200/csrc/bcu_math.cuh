@@ -51,41 +51,32 @@ BCU_HD_NOINLINE cplx c_div(cplx n, cplx dd) {
     const double RMIN2 = 2.220446049250313e-16;
     const double RMINSCAL = 1 / 2.220446049250313e-16;
     const double RMAX2 = RBIG * RMIN2;
-    double denom, ratio, x, y;
-    if (fabs(c) < fabs(d)) {
-        if (fabs(d) >= RBIG) { a = a / 2; b = b / 2; c = c / 2; d = d / 2; }
-        if (fabs(d) < RMIN2) {
-            a = a * RMINSCAL; b = b * RMINSCAL; c = c * RMINSCAL; d = d * RMINSCAL;
-        } else if (((fabs(a) < RMIN) && (fabs(b) < RMAX2) && (fabs(d) < RMAX2)) ||
-                   ((fabs(b) < RMIN) && (fabs(a) < RMAX2) && (fabs(d) < RMAX2))) {
-            a = a * RMINSCAL; b = b * RMINSCAL; c = c * RMINSCAL; d = d * RMINSCAL;
-        }
-        ratio = c / d;
-        denom = (c * ratio) + d;
-        if (fabs(ratio) > RMIN) {
-            x = ((a * ratio) + b) / denom;
-            y = ((b * ratio) - a) / denom;
-        } else {
-            x = ((c * (a / d)) + b) / denom;
-            y = ((c * (b / d)) - a) / denom;
-        }
+    // The two arms of Smith's algorithm (|c| < |d| and not) are mirror images; here they share one instruction stream
+    // with the operands swapped by selects (lanes of a warp take both arms about equally often):
+    //   arm 1 (|c| < |d|): ratio = c/d, denom = c*ratio + d, x = (a*ratio + b)/denom, y = (b*ratio - a)/denom
+    //   arm 2            : ratio = d/c, denom = d*ratio + c, x = (b*ratio + a)/denom, y = (b - a*ratio)/denom
+    // (y of arm 1 is t - a with t = b*ratio, y of arm 2 is b - t with t = a*ratio: the same subtraction, operands swapped.)
+    const bool arm1 = fabs(c) < fabs(d);
+    double lo = arm1 ? c : d, hi = arm1 ? d : c;   // |lo| <= |hi| (arm 2 also takes |c| == |d|)
+    if (fabs(hi) >= RBIG) { a = a / 2; b = b / 2; lo = lo / 2; hi = hi / 2; }
+    if (fabs(hi) < RMIN2) {
+        a = a * RMINSCAL; b = b * RMINSCAL; lo = lo * RMINSCAL; hi = hi * RMINSCAL;
+    } else if (((fabs(a) < RMIN) && (fabs(b) < RMAX2) && (fabs(hi) < RMAX2)) ||
+               ((fabs(b) < RMIN) && (fabs(a) < RMAX2) && (fabs(hi) < RMAX2))) {
+        a = a * RMINSCAL; b = b * RMINSCAL; lo = lo * RMINSCAL; hi = hi * RMINSCAL;
+    }
+    const double u = arm1 ? a : b, v = arm1 ? b : a;   // x = (u*ratio + v) / denom
+    const double ratio = lo / hi;
+    const double denom = (lo * ratio) + hi;
+    double x, y;
+    if (fabs(ratio) > RMIN) {
+        const double t = v * ratio;
+        x = ((u * ratio) + v) / denom;
+        y = (arm1 ? (t - u) : (u - t)) / denom;
     } else {
-        if (fabs(c) >= RBIG) { a = a / 2; b = b / 2; c = c / 2; d = d / 2; }
-        if (fabs(c) < RMIN2) {
-            a = a * RMINSCAL; b = b * RMINSCAL; c = c * RMINSCAL; d = d * RMINSCAL;
-        } else if (((fabs(a) < RMIN) && (fabs(b) < RMAX2) && (fabs(c) < RMAX2)) ||
-                   ((fabs(b) < RMIN) && (fabs(a) < RMAX2) && (fabs(c) < RMAX2))) {
-            a = a * RMINSCAL; b = b * RMINSCAL; c = c * RMINSCAL; d = d * RMINSCAL;
-        }
-        ratio = d / c;
-        denom = (d * ratio) + c;
-        if (fabs(ratio) > RMIN) {
-            x = ((b * ratio) + a) / denom;
-            y = (b - (a * ratio)) / denom;
-        } else {
-            x = ((d * (b / c)) + a) / denom;
-            y = (b - (d * (a / c))) / denom;
-        }
+        const double t = lo * (v / hi);
+        x = ((lo * (u / hi)) + v) / denom;
+        y = (arm1 ? (t - u) : (u - t)) / denom;
     }
     // Annex-G infinity/zero recovery (both parts NaN) is not reproduced; see c_mul.
     return c_make(x, y);
@@ -109,17 +100,15 @@ BCU_HD double g_hypot(double x, double y) {
     } else if (ax * EPS >= ay) {
         return ax + ay;
     }
-    double t1, t2;
     double h = sqrt(ax * ax + ay * ay);
-    if (h <= 2.0 * ay) {
-        double delta = h - ay;
-        t1 = ax * (2.0 * delta - ax);
-        t2 = (delta - 2.0 * (ax - ay)) * delta;
-    } else {
-        double delta = h - ax;
-        t1 = 2.0 * delta * (ax - 2.0 * ay);
-        t2 = (4.0 * delta - ay) * ay + delta * delta;
-    }
+    // both correction formulas are evaluated and one is selected (no divergent branch; identical operations)
+    const bool small = h <= 2.0 * ay;
+    const double delta = h - (small ? ay : ax);
+    const double t1a = ax * (2.0 * delta - ax);
+    const double t2a = (delta - 2.0 * (ax - ay)) * delta;
+    const double t1b = 2.0 * delta * (ax - 2.0 * ay);
+    const double t2b = (4.0 * delta - ay) * ay + delta * delta;
+    const double t1 = small ? t1a : t1b, t2 = small ? t2a : t2b;
     h -= (t1 + t2) / (2.0 * h);
     return scaleBack == 1.0 ? h : h * scaleBack;
 }
@@ -160,14 +149,15 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
         x.re = x.re * 0x1p+54; x.im = x.im * 0x1p+54;
     }
     d = g_hypot(x.re, x.im);
-    if (x.re > 0) {
-        r = sqrt(0.5 * (d + x.re));
-        if (scale == 1 && fabs(x.im) < 1) { s = x.im / r; r = r * 2.0; scale = 0; }
-        else s = 0.5 * (x.im / r);
-    } else {
-        s = sqrt(0.5 * (d - x.re));
-        if (scale == 1 && fabs(x.im) < 1) { r = fabs(x.im / s); s = s * 2.0; scale = 0; }
-        else r = fabs(0.5 * (x.im / s));
+    {
+        // re > 0:  r = sqrt(0.5 (d + re)), s = 0.5 (im / r);   re < 0:  s = sqrt(0.5 (d - re)), r = |0.5 (im / s)|.
+        // d - re with re < 0 is d + |re|, so both arms are  t = sqrt(0.5 (d + |re|)), u = 0.5 (im / t)  with roles swapped.
+        const bool pos = x.re > 0;
+        double t = sqrt(0.5 * (d + fabs(x.re))), u;
+        if (scale == 1 && fabs(x.im) < 1) { u = x.im / t; t = t * 2.0; scale = 0; }
+        else u = 0.5 * (x.im / t);
+        r = pos ? t : fabs(u);
+        s = pos ? u : t;
     }
     if (scale == 1) { r = r * 2.0; s = s * 2.0; }
     else if (scale != 0) { r = r * 0x1p-27; s = s * 0x1p-27; }
@@ -179,31 +169,40 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
 // glibc sysdeps/ieee754/dbl-64/x2y2m1.c: x*x + y*y - 1 with exact products and a sorted,
 // error-free summation.  The exact low product word is the same whether produced by Dekker
 // splitting (glibc's generic build) or by an FMA (here).
+BCU_HD void x2y2m1_cswap(double& a, double& b) {   // one step of a stable insertion sort on |.|
+    const bool sw = fabs(a) > fabs(b);
+    const double t = a;
+    a = sw ? b : a;
+    b = sw ? t : b;
+}
 BCU_HD double g_x2y2m1(double x, double y) {
-    double v[5];
-    v[1] = x * x; v[0] = bcu_fma(x, x, -v[1]);
-    v[3] = y * y; v[2] = bcu_fma(y, y, -v[3]);
-    v[4] = -1.0;
-    // insertion sort by |.| ascending (qsort with compare on absolute values)
-    for (int i = 1; i < 5; ++i) {
-        double k = v[i];
-        int j = i - 1;
-        while (j >= 0 && fabs(v[j]) > fabs(k)) { v[j + 1] = v[j]; --j; }
-        v[j + 1] = k;
-    }
-    for (int i = 0; i <= 3; ++i) {
-        // add_split(&v[i+1], &v[i], v[i+1], v[i])
-        double hi = v[i + 1] + v[i];
-        double lo = (v[i + 1] - hi) + v[i];
-        v[i + 1] = hi; v[i] = lo;
-        for (int a = i + 2; a < 5; ++a) {
-            double k = v[a];
-            int j = a - 1;
-            while (j >= i + 1 && fabs(v[j]) > fabs(k)) { v[j + 1] = v[j]; --j; }
-            v[j + 1] = k;
-        }
-    }
-    return v[4] + v[3] + v[2] + v[1] + v[0];
+    double v0, v1, v2, v3, v4;
+    v1 = x * x; v0 = bcu_fma(x, x, -v1);
+    v3 = y * y; v2 = bcu_fma(y, y, -v3);
+    v4 = -1.0;
+    // glibc sorts by |.| ascending (qsort) and re-sorts the tail after every add_split.  An insertion sort is a fixed
+    // sequence of adjacent compare-exchanges (the ones after the insertion point are no-ops), so it runs in registers
+    // without a branch; strict '>' keeps equal magnitudes in their order, as the array version did.
+    x2y2m1_cswap(v0, v1);
+    x2y2m1_cswap(v1, v2); x2y2m1_cswap(v0, v1);
+    x2y2m1_cswap(v2, v3); x2y2m1_cswap(v1, v2); x2y2m1_cswap(v0, v1);
+    x2y2m1_cswap(v3, v4); x2y2m1_cswap(v2, v3); x2y2m1_cswap(v1, v2); x2y2m1_cswap(v0, v1);
+    double hi;
+    // i = 0: add_split(v1, v0), re-sort v1..v4
+    hi = v1 + v0; v0 = (v1 - hi) + v0; v1 = hi;
+    x2y2m1_cswap(v1, v2);
+    x2y2m1_cswap(v2, v3); x2y2m1_cswap(v1, v2);
+    x2y2m1_cswap(v3, v4); x2y2m1_cswap(v2, v3); x2y2m1_cswap(v1, v2);
+    // i = 1: add_split(v2, v1), re-sort v2..v4
+    hi = v2 + v1; v1 = (v2 - hi) + v1; v2 = hi;
+    x2y2m1_cswap(v2, v3);
+    x2y2m1_cswap(v3, v4); x2y2m1_cswap(v2, v3);
+    // i = 2: add_split(v3, v2), re-sort v3..v4
+    hi = v3 + v2; v2 = (v3 - hi) + v2; v3 = hi;
+    x2y2m1_cswap(v3, v4);
+    // i = 3: add_split(v4, v3)
+    hi = v4 + v3; v3 = (v4 - hi) + v3; v4 = hi;
+    return v4 + v3 + v2 + v1 + v0;
 }
 
 // glibc math/s_clog_template.c, finite non-zero operand.
