@@ -52,6 +52,16 @@ BCU_HD double u2d(uint64_t u) {
 #endif
 }
 
+// n / d.  The device's IEEE division leaves its inline fast path for a ~100-instruction subroutine whenever the quotient is
+// zero or subnormal, and this solver divides exact zeros all the time (real inputs carried as complex numbers with a zero
+// imaginary part).  0 / d for a non-zero, non-NaN d is a zero with the XOR of the signs -- returned directly.
+BCU_HD double bcu_div(double n, double d) {
+#if defined(__CUDA_ARCH__)
+    if (n == 0.0 && d == d && d != 0.0) return u2d((d2u(n) ^ d2u(d)) & 0x8000000000000000ull);
+#endif
+    return n / d;
+}
+
 // ---- tables -------------------------------------------------------------------------------------------------
 #include "bcu_libm_tables.inc"
 

@@ -66,17 +66,17 @@ BCU_HD_NOINLINE cplx c_div(cplx n, cplx dd) {
         a = a * RMINSCAL; b = b * RMINSCAL; lo = lo * RMINSCAL; hi = hi * RMINSCAL;
     }
     const double u = arm1 ? a : b, v = arm1 ? b : a;   // x = (u*ratio + v) / denom
-    const double ratio = lo / hi;
+    const double ratio = bcu_div(lo, hi);
     const double denom = (lo * ratio) + hi;
     double x, y;
     if (fabs(ratio) > RMIN) {
         const double t = v * ratio;
-        x = ((u * ratio) + v) / denom;
-        y = (arm1 ? (t - u) : (u - t)) / denom;
+        x = bcu_div((u * ratio) + v, denom);
+        y = bcu_div(arm1 ? (t - u) : (u - t), denom);
     } else {
-        const double t = lo * (v / hi);
-        x = ((lo * (u / hi)) + v) / denom;
-        y = (arm1 ? (t - u) : (u - t)) / denom;
+        const double t = lo * bcu_div(v, hi);
+        x = bcu_div((lo * bcu_div(u, hi)) + v, denom);
+        y = bcu_div(arm1 ? (t - u) : (u - t), denom);
     }
     // Annex-G infinity/zero recovery (both parts NaN) is not reproduced; see c_mul.
     return c_make(x, y);
@@ -109,7 +109,7 @@ BCU_HD double g_hypot(double x, double y) {
     const double t1b = 2.0 * delta * (ax - 2.0 * ay);
     const double t2b = (4.0 * delta - ay) * ay + delta * delta;
     const double t1 = small ? t1a : t1b, t2 = small ? t2a : t2b;
-    h -= (t1 + t2) / (2.0 * h);
+    h -= bcu_div(t1 + t2, 2.0 * h);
     return scaleBack == 1.0 ? h : h * scaleBack;
 }
 
@@ -154,8 +154,8 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
         // d - re with re < 0 is d + |re|, so both arms are  t = sqrt(0.5 (d + |re|)), u = 0.5 (im / t)  with roles swapped.
         const bool pos = x.re > 0;
         double t = sqrt(0.5 * (d + fabs(x.re))), u;
-        if (scale == 1 && fabs(x.im) < 1) { u = x.im / t; t = t * 2.0; scale = 0; }
-        else u = 0.5 * (x.im / t);
+        if (scale == 1 && fabs(x.im) < 1) { u = bcu_div(x.im, t); t = t * 2.0; scale = 0; }
+        else u = 0.5 * bcu_div(x.im, t);
         r = pos ? t : fabs(u);
         s = pos ? u : t;
     }
