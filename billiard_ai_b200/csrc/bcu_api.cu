@@ -88,7 +88,7 @@ struct bcu_engine {
     bool useGraph = true;               // BCU_NO_GRAPH / BCU_ROUND_TIMING: plain stream launches
     cudaGraphExec_t pipeGraph = nullptr;
     PipeGraphKey pipeKey{};
-    int kernelVersion = 4;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
+    int kernelVersion = 3;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
     // top-k
     DevBuf<unsigned char> dTopkScratch;
     DevBuf<uint64_t> dTopCost, dTopId;
@@ -237,7 +237,7 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     upload_constants(e->table, e->rules, e->stream);
     e->maxCtas = simulate_max_ctas(device);
     cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
-    if (const char* kv = getenv("BCU_KERNEL")) e->kernelVersion = atoi(kv) == 2 ? 2 : atoi(kv) == 3 ? 3 : 4;
+    if (const char* kv = getenv("BCU_KERNEL")) e->kernelVersion = atoi(kv) == 2 ? 2 : 3;
     if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
     if (const char* sv = getenv("BCU_STREAMS")) {
         const int v = atoi(sv);
@@ -343,13 +343,6 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
     if (trace || e->kernelVersion == 2) {
         CK(e->dNextCand.reserve(1));
         CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
-        e->launches++;
-    } else if (e->kernelVersion == 4) {
-        // batch path: the persistent tile kernel (bcu_tile.cu); parameters are read from device memory
-        CK(e->dPipeParams.reserve(PIPE_MAX_STREAMS));
-        CK(e->dNextCand.reserve(1));
-        CK(cudaMemcpyAsync(e->dPipeParams.p, &p, sizeof(LaunchParams), cudaMemcpyHostToDevice, e->stream));
-        CK(launch_tile(e->dPipeParams.p, p.nCand, p.states.nBalls, e->sms, e->dNextCand.p, e->stream));
         e->launches++;
     } else {
         // batch path: the event-synchronous pipeline.  A launch is cut into parts that run on separate streams: every

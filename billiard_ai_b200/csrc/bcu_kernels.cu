@@ -886,7 +886,6 @@ void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream
     cudaMemcpyToSymbolAsync(c_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
     cudaMemcpyToSymbolAsync(c_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
     pipeline_upload_constants(table, rules, stream);
-    tile_upload_constants(table, rules, stream);
     cudaStreamSynchronize(stream);
 }
 

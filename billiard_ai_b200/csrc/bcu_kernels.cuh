@@ -88,12 +88,6 @@ cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, bool withCo
                             cudaStream_t stream, bool resetOverflow);
 int pipeline_launch_count();
 
-// ---- K1 v4, the persistent tile kernel (bcu_tile.cu) --------------------------------------------------------------
-constexpr int TILE_SLOTS = 64;   // strikes in flight per CTA (slots x balls must stay below 2048: 11-bit entry index)
-void tile_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
-cudaError_t launch_tile(const LaunchParams* dParams, int64_t nCand, int nBalls, int sms, unsigned long long* nextCand,
-                        cudaStream_t stream);
-
 void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
 cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, unsigned long long* nextCand, cudaStream_t stream);
 int simulate_max_ctas(int device);

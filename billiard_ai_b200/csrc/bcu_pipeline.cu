@@ -566,15 +566,27 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, bool withCounters
         if (!timing) return;
         cudaEvent_t x; cudaEventCreate(&x); cudaEventRecord(x, stream); ev.push_back(x);
     };
+    // persistent grids: exactly one resident wave of every kernel
+    static int occItems = 0, occQuartic = 0, occApply = 0;
+    static size_t occSmem = ~(size_t)0;
+    if (occSmem != itemSmem) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occItems, items_kernel, ITEM_BLOCK, itemSmem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occQuartic, quartic_kernel, QUARTIC_BLOCK, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occApply, apply_kernel, APPLY_BLOCK, 0);
+        if (occItems < 1) occItems = 1;
+        if (occQuartic < 1) occQuartic = 1;
+        if (occApply < 1) occApply = 1;
+        occSmem = itemSmem;
+    }
     mark();
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     mark();
     for (int r = 0; r < ROUNDS; ++r) {
-        items_kernel<<<sms * 8, ITEM_BLOCK, itemSmem, stream>>>(p, w, r);
+        items_kernel<<<sms * occItems, ITEM_BLOCK, itemSmem, stream>>>(p, w, r);
         mark();
-        quartic_kernel<<<sms * 4, QUARTIC_BLOCK, 0, stream>>>(w, r);
+        quartic_kernel<<<sms * occQuartic, QUARTIC_BLOCK, 0, stream>>>(w, r);
         mark();
-        apply_kernel<<<sms * 4, APPLY_BLOCK, 0, stream>>>(p, w, r);
+        apply_kernel<<<sms * occApply, APPLY_BLOCK, 0, stream>>>(p, w, r);
         mark();
     }
     finish_kernel<<<(unsigned)(finBlocks < sms * 8 ? finBlocks : sms * 8), 256, 0, stream>>>(p, w);
