@@ -267,7 +267,8 @@ def run_b200(args, rank, local_rank, world):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (simulate_candidates) -----------------------------------------------
+    # ---- roofline of the simulate stage: the strike pipeline's kernels (items / quartic / apply per event round), timed
+    #      together with CUDA events on the engine's stream; its FP64 work is the quartic kernel's ------------------------
     k_ms = float(np.mean(kernel_ms))
     per_rank = cvec.cpu().numpy() / world
     fp64_flop = per_rank[2] * W_QUARTIC_FP64
@@ -283,7 +284,7 @@ def run_b200(args, rank, local_rank, world):
     except Exception:
         hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
     ach = fp64_flop / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "fp64_vector", "kernel": "simulate_candidates", "achieved": ach, "peak": peak_dp,
+    roofline = {"bound": "fp64_vector", "kernel": "strike pipeline (init + 31 x {items, quartic, apply} + finish; FP64 work = quartic_kernel)", "achieved": ach, "peak": peak_dp,
                 "unit": "GFLOP/s", "frac": ach / peak_dp, "traffic": None,
                 "peak_source": "measured in this run: un-fused DADD+DMUL issue rate (FMA contraction is forbidden on "
                                "this path); DFMA rate x2 listed for context",
