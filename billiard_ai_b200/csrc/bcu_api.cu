@@ -536,7 +536,7 @@ int bcu_topk(bcu_engine* e, int32_t k, uint64_t* outCost, uint64_t* outId, int32
     CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
     CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
                    e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
-    e->launches += 2;
+    e->launches += 3;
     int32_t valid = 0;
     CK(cudaMemcpyAsync(outCost, e->dTopCost.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(outId, e->dTopId.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
@@ -606,7 +606,7 @@ static int topk_device(bcu_engine* e, int32_t k) {
     CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
     CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
                    e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
-    e->launches += 2;
+    e->launches += 3;
     return BCU_OK;
 }
 
