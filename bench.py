@@ -241,7 +241,7 @@ def run_b200(args, rank, local_rank, world):
 
     def e2e_step():
         eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"])
-        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=True, event_log=False)
+        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=True, event_log=False, reuse_buffers=True)
         eng.level_select(BEAM)
         b = eng.fetch_beam()
         return res, b

@@ -277,6 +277,12 @@ void bcu_destroy(bcu_engine* e) {
     delete e;
 }
 
+int bcu_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return BCU_ERR_INVALID;
+    return cudaHostAlloc(out, bytes, cudaHostAllocDefault) == cudaSuccess ? BCU_OK : BCU_ERR_CUDA;
+}
+int bcu_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? BCU_OK : BCU_ERR_CUDA; }
+
 const char* bcu_last_error(const bcu_engine* e) { return e ? e->err.c_str() : "null engine"; }
 
 int bcu_get_rail_derived(const bcu_engine* e, float* out6) {

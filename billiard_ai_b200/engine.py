@@ -64,6 +64,8 @@ def load_library(path=None):
     lib.bcu_launch_count.argtypes = [C.c_void_p]
     lib.bcu_destroy.argtypes = [C.c_void_p]
     lib.bcu_destroy.restype = None
+    lib.bcu_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.bcu_host_free.argtypes = [C.c_void_p]
     if path is None:
         _lib = lib
     return lib
@@ -98,6 +100,8 @@ class Engine:
         self.n_states = 0
         self._last_n = 0
         self._beam_k = 0
+        self._pinned = []
+        self._result_cache = {}
 
     @classmethod
     def from_table(cls, tbl, scores, cue_type=0, device=0):
@@ -112,6 +116,10 @@ class Engine:
         if getattr(self, "h", None):
             self.lib.bcu_destroy(self.h)
             self.h = None
+            self._result_cache = {}
+            for ptr in self._pinned:
+                self.lib.bcu_host_free(ptr)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -147,11 +155,31 @@ class Engine:
         self.n_states, self.n_balls = ns, nb
 
     # ---- explicit candidates ----------------------------------------------------------------------
-    def _result_buffers(self, n, final_pos, event_log):
-        out = dict(cost=np.zeros(n, np.uint64), flags=np.zeros(n, np.uint32), potted=np.zeros(n, np.uint32),
-                   final_time=np.zeros(n, np.float32),
-                   final_pos=np.zeros((n, self.n_balls, 2), np.float32) if final_pos else None,
-                   event_log=np.full((n, 32, 4), -1, np.int32) if event_log else None)
+    def pinned_array(self, shape, dtype):
+        """numpy array over page-locked host memory (bcu_host_alloc); freed when the engine is closed."""
+        dtype = np.dtype(dtype)
+        count = int(np.prod(shape))
+        ptr = C.c_void_p()
+        self._ck(self.lib.bcu_host_alloc(C.c_size_t(max(1, count) * dtype.itemsize), C.byref(ptr)), "bcu_host_alloc")
+        self._pinned.append(ptr)
+        buf = (C.c_char * (max(1, count) * dtype.itemsize)).from_address(ptr.value)
+        return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+    def _result_buffers(self, n, final_pos, event_log, reuse=False):
+        if reuse:   # one cached set of pinned buffers per shape: the previous call's results are overwritten
+            key = (n, self.n_balls, bool(final_pos), bool(event_log))
+            if key not in self._result_cache:
+                self._result_cache[key] = dict(
+                    cost=self.pinned_array(n, np.uint64), flags=self.pinned_array(n, np.uint32),
+                    potted=self.pinned_array(n, np.uint32), final_time=self.pinned_array(n, np.float32),
+                    final_pos=self.pinned_array((n, self.n_balls, 2), np.float32) if final_pos else None,
+                    event_log=self.pinned_array((n, 32, 4), np.int32) if event_log else None)
+            out = dict(self._result_cache[key])
+        else:
+            out = dict(cost=np.zeros(n, np.uint64), flags=np.zeros(n, np.uint32), potted=np.zeros(n, np.uint32),
+                       final_time=np.zeros(n, np.float32),
+                       final_pos=np.zeros((n, self.n_balls, 2), np.float32) if final_pos else None,
+                       event_log=np.full((n, 32, 4), -1, np.int32) if event_log else None)
         res = _Results(_p(out["cost"], C.c_uint64), _p(out["flags"], C.c_uint32), _p(out["potted"], C.c_uint32),
                        _p(out["final_time"], C.c_float),
                        _p(out["final_pos"], C.c_float) if final_pos else _null(C.c_float),
@@ -164,14 +192,15 @@ class Engine:
         out["flags"] = out["flags"] & 0xff
         return out
 
-    def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False):
+    def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False, reuse_buffers=False):
+        """reuse_buffers=True returns views of cached page-locked result buffers (overwritten by the next such call)."""
         vx = np.ascontiguousarray(vx, dtype=np.float32)
         vy = np.ascontiguousarray(vy, dtype=np.float32)
         n = len(vx)
         cs = np.ascontiguousarray(np.broadcast_to(np.asarray(cand_state, dtype=np.int32), (n,)))
         sc = np.ascontiguousarray(np.broadcast_to(np.asarray(search_cost, dtype=np.uint64), (n,)))
         bc = np.ascontiguousarray(np.broadcast_to(np.asarray(base_cost, dtype=np.uint64), (n,)))
-        out, res = self._result_buffers(n, final_pos, event_log)
+        out, res = self._result_buffers(n, final_pos, event_log, reuse=reuse_buffers)
         self._ck(self.lib.bcu_evaluate(self.h, C.c_int64(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
                                        _p(sc, C.c_uint64), _p(bc, C.c_uint64), C.byref(res)), "bcu_evaluate")
         self._last_n = n

@@ -15,6 +15,7 @@
 #ifndef BILLIARD_CUDA_H
 #define BILLIARD_CUDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -90,6 +91,11 @@ const char* bcu_last_error(const bcu_engine* e);
 const char* bcu_version(void);
 /* derived rail geometry as uploaded: n_rails x {normal.xy, shiftedStart.xy, shiftedEnd.xy} */
 int bcu_get_rail_derived(const bcu_engine* e, float* out6);
+
+/* Page-locked host memory for candidate / result buffers (cudaHostAlloc): copies from and to such buffers run at full
+ * PCIe speed and asynchronously; any host pointer is accepted by the calls below, pinned ones are just faster. */
+int bcu_host_alloc(size_t bytes, void** out);
+int bcu_host_free(void* p);
 
 /* ---- table states (the beam) ------------------------------------------------------------------------
  * pos [n_states][n_balls][2]; types [n_states][n_balls] (type code, -1 = no ball);
