@@ -144,13 +144,19 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
                     const uint32_t en = sEnt[c2 >> 5];
                     const int o = (int)(c2 & 31u), b = (int)(en & 31u);
                     const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
-                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], x2 = w.pos[g2], y2 = w.vel[g2];
+                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], n1 = w.vn[g1], x2 = w.pos[g2], y2 = w.vel[g2], n2 = w.vn[g2];
                     const v2 p1 = mk(x1.x, x1.y), v1 = mk(y1.x, y1.y), p2 = mk(x2.x, x2.y), w2 = mk(y2.x, y2.y);
+                    const v2 v1n = mk(n1.x, n1.y), w2n = mk(n2.x, n2.y);
                     // the reference tests b -> o and, on o's own turn, o -> b; the quantised coefficients of both
                     // orders are identical, so one job covers both
                     #pragma unroll 1
-                    for (int turn = 0; turn < 2 && !pass; ++turn)   // one call site, operands swapped by select
-                        pass = collision_precheck(turn ? w2 : v1, turn ? p2 : p1, turn ? v1 : w2, turn ? p1 : p2, diameter);
+                    for (int turn = 0; turn < 2 && !pass; ++turn) {   // one call site each, operands swapped by select
+                        const v2 va = turn ? w2 : v1, pa = turn ? p2 : p1, van = turn ? w2n : v1n;
+                        const v2 vb = turn ? v1 : w2, pb = turn ? p1 : p2, vbn = turn ? v1n : w2n;
+                        if (is_zero(va)) continue;                                  // :287
+                        if (dot(vb, vb) > 0) pass = collision_precheck_moving(va, pa, van, vb, pb, vbn, diameter);
+                        else pass = !(point_to_half_line_sq(pa, va, pb) > diameter * diameter);   // :318-324
+                    }
                     code = ((c2 >> 5) << 6) | 32u | (uint32_t)o;
                 }
                 const unsigned m = __ballot_sync(FULL, pass);

@@ -165,6 +165,24 @@ BCU_HD bool collision_precheck(v2 v1, v2 p1, v2 v2_, v2 p2, float diameter) {
     return true;
 }
 
+// The moving-vs-moving arm of the same pre-checks (:292-317) with the normalised velocities passed in: a ball's stored
+// velocityNormed (state::BallState, type.cpp:176-184) is glm::normalize(velocity), the very value the reference recomputes
+// here, so the two square roots and divisions per call are saved without changing a bit.  Both velocities are non-zero.
+BCU_HD bool collision_precheck_moving(v2 v1, v2 p1, v2 v1n, v2 v2_, v2 p2, v2 v2n, float diameter) {
+    if (!half_lines_intersect(p1, v1, p2, v2_)) {
+        v2 from1To2 = p2 - p1;
+        v2 offset = from1To2 - v1n * dot(from1To2, v1n);
+        v2 back1 = v1n * -diameter;
+        v2 back2 = v2n * -diameter;
+        if (!half_lines_intersect(p1 + offset + back1, v1, p2 + back2, v2_)) {
+            float velocityDistance = dot(v1n, v2n);
+            float offsetSq = dot(offset, offset);
+            if (velocityDistance != 1 && offsetSq > diameter * diameter) return false;
+        }
+    }
+    return true;
+}
+
 // Quantised quartic coefficients of physics::timeToCollision (:326-337).
 BCU_HD void collision_coefficients(v2 a1, v2 v1, v2 p1, v2 a2, v2 v2_, v2 p2, float diameter, float co[5]) {
     float toMeter = 1.0f / 1000.0f;
