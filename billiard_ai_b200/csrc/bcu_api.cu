@@ -52,7 +52,6 @@ struct bcu_engine {
     TableGeom table;
     RulesData rules;
     std::vector<float> railDerived;
-    int maxCtas = 148;
     int64_t launches = 0;
     bool countersOn = false;
 
@@ -75,7 +74,9 @@ struct bcu_engine {
     DevBuf<float> dFinalTime, dFinalPos;
     DevBuf<int4> dEventLog;
     DevBuf<float> dTraceTimes, dTraceRec;
-    DevBuf<unsigned long long> dCounters, dNextCand;
+    DevBuf<unsigned long long> dCounters;
+    DevBuf<TableGeom> dTable;        // this engine's table geometry and rules, read by the kernels through LaunchParams
+    DevBuf<RulesData> dRules;
     DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
     int sms = 148;
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
@@ -88,7 +89,6 @@ struct bcu_engine {
     bool useGraph = true;               // BCU_NO_GRAPH / BCU_ROUND_TIMING: plain stream launches
     cudaGraphExec_t pipeGraph = nullptr;
     PipeGraphKey pipeKey{};
-    int kernelVersion = 3;           // BCU_KERNEL=2 selects the warp-per-strike kernel (A/B measurements only)
     // top-k
     DevBuf<unsigned char> dTopkScratch;
     DevBuf<uint64_t> dTopCost, dTopId;
@@ -234,11 +234,20 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
         delete e;
         return BCU_ERR_CUDA;
     }
-    upload_constants(e->table, e->rules, e->stream);
-    e->maxCtas = simulate_max_ctas(device);
+    upload_constants(e->stream);
+    if (e->dTable.reserve(1) != cudaSuccess || e->dRules.reserve(1) != cudaSuccess ||
+        cudaMemcpyAsync(e->dTable.p, &e->table, sizeof(TableGeom), cudaMemcpyHostToDevice, e->stream) != cudaSuccess ||
+        cudaMemcpyAsync(e->dRules.p, &e->rules, sizeof(RulesData), cudaMemcpyHostToDevice, e->stream) != cudaSuccess ||
+        cudaStreamSynchronize(e->stream) != cudaSuccess) {
+        delete e;
+        return BCU_ERR_CUDA;
+    }
     cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
-    if (const char* kv = getenv("BCU_KERNEL")) e->kernelVersion = atoi(kv) == 2 ? 2 : 3;
     if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
+    if (const char* jv = getenv("BCU_JOBS_PER_STRIKE")) {   // initial quartic-queue capacity (tests force the overflow path)
+        const int v = atoi(jv);
+        e->jobsPerStrike = v < 1 ? 1 : v > 1024 ? 1024 : v;
+    }
     if (const char* sv = getenv("BCU_STREAMS")) {
         const int v = atoi(sv);
         e->pipeStreams = v < 1 ? 1 : v > PIPE_MAX_STREAMS ? PIPE_MAX_STREAMS : v;
@@ -256,7 +265,8 @@ void bcu_destroy(bcu_engine* e) {
     e->dCandState.release(); e->dVx.release(); e->dVy.release(); e->dSearchCost.release(); e->dBaseCost.release();
     e->dDirs.release(); e->dSpeeds.release();
     e->dCost.release(); e->dFlags.release(); e->dPotted.release(); e->dFinalTime.release(); e->dFinalPos.release();
-    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dNextCand.release(); e->dPipeWs.release();
+    e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dPipeWs.release();
+    e->dTable.release(); e->dRules.release();
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
@@ -334,6 +344,7 @@ static int reserve_results(bcu_engine* e, int64_t n, bool wantPos, bool wantLog)
 static void fill_common(bcu_engine* e, LaunchParams& p, int64_t n, bool wantPos, bool wantLog) {
     std::memset(&p, 0, sizeof(p));
     p.nCand = n;
+    p.table = e->dTable.p; p.rules = e->dRules.p;
     p.states.nStates = e->nStates; p.states.nBalls = e->nBalls;
     p.states.pos = e->dStatePos.p; p.states.type = e->dStateType.p; p.states.expectedMask = e->dExpected.p;
     p.out.cost = e->dCost.p; p.out.flags = e->dFlags.p; p.out.potted = e->dPotted.p; p.out.finalTime = e->dFinalTime.p;
@@ -344,11 +355,10 @@ static void fill_common(bcu_engine* e, LaunchParams& p, int64_t n, bool wantPos,
 
 static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
     if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
-    if (p.out.eventLog) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
+    if (p.out.eventLog && trace) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
     CK(cudaEventRecord(e->evStart, e->stream));
-    if (trace || e->kernelVersion == 2) {
-        CK(e->dNextCand.reserve(1));
-        CK(launch_simulate(p, trace, e->maxCtas, e->dNextCand.p, e->stream));
+    if (trace) {
+        CK(launch_trace(p, e->stream));
         e->launches++;
     } else {
         // batch path: the event-synchronous pipeline.  A launch is cut into parts that run on separate streams: every
@@ -396,6 +406,12 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
                     hp[g] = q;
                 }
                 CK(cudaMemcpyAsync(e->dPipeParams.p, hp, G * sizeof(LaunchParams), cudaMemcpyHostToDevice, e->stream));
+                if (p.out.eventLog) {   // -1 padding of this wave's logs (again on a retry: a run that overflowed logged
+                                        // events of strikes that went wrong)
+                    const int64_t off = wave * per;
+                    const int64_t cnt = p.nCand - off < (int64_t)G * per ? p.nCand - off : (int64_t)G * per;
+                    CK(cudaMemsetAsync(p.out.eventLog + (size_t)off * 32, 0xff, (size_t)cnt * 32 * sizeof(int4), e->stream));
+                }
                 PipeGraphKey key{e->dPipeWs.p, e->dPipeParams.p, per, G, nBalls, e->jobsPerStrike, withCounters};
                 const bool useGraph = e->useGraph;
                 if (!useGraph || !e->pipeGraph || !(key == e->pipeKey)) {
@@ -407,7 +423,7 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
                         ws.base = e->dPipeWs.p + wsBytes * g;
                         pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, &ws);
                         CK(cudaStreamWaitEvent(e->pipeStream[g], e->pipeFork, 0));
-                        CK(launch_pipeline(e->dPipeParams.p + g, nBalls, withCounters, ws, e->sms, e->pipeStream[g], true));
+                        CK(launch_pipeline(e->dPipeParams.p + g, nBalls, e->table.nRails, e->table.nPockets, withCounters, ws, e->sms, e->pipeStream[g], true));
                         // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
                         CK(cudaMemcpyAsync(e->hOverflow + g, pipeline_overflow_flag(ws), sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                            e->pipeStream[g]));

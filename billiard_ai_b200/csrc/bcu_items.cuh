@@ -55,15 +55,15 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
     __shared__ PocketGeom sPockets[MAX_POCKETS];
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int R = p_table.nRails, P = p_table.nPockets, NB = p.states.nBalls;
+    const int R = p.table->nRails, P = p.table->nPockets, NB = p.states.nBalls;
     const uint32_t nDyn = w.counts[4 * round + 1];
     if (nDyn == 0) return;
     for (int i = tid; i < R; i += ITEM_BLOCK) {
-        const RailGeom rg = p_table.rails[i];
+        const RailGeom rg = p.table->rails[i];
         sRails[i] = rg;
         sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
     }
-    for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p_table.pockets[i];
+    for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p.table->pockets[i];
     uint16_t* qRails = smemQ;
     uint16_t* qPockets = qRails + ITEM_BLOCK * R;
     uint16_t* qPairs = qPockets + ITEM_BLOCK * P;
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
     const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
     unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
     uint32_t* jobCount = &w.counts[4 * round + 2];
-    const float diameter = p_table.diameter;
+    const float diameter = p.table->diameter;
     const float dd = diameter * diameter;
 
     for (uint32_t base = blockIdx.x * ITEM_BLOCK; base < nDyn; base += gridDim.x * ITEM_BLOCK) {

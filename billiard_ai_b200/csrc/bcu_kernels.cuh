@@ -47,6 +47,8 @@ struct Results {
 
 struct LaunchParams {
     int64_t nCand;
+    const TableGeom* table;    // device copies owned by the engine (nothing table- or rules-specific is process-global)
+    const RulesData* rules;
     CandidateSource src;
     StateTable states;
     Results out;
@@ -83,14 +85,13 @@ struct PipeWorkspace {
 };
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
-void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
-cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, bool withCounters, const PipeWorkspace& w, int sms,
-                            cudaStream_t stream, bool resetOverflow);
+void pipeline_upload_constants(cudaStream_t stream);
+cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, int nRails, int nPockets, bool withCounters,
+                            const PipeWorkspace& w, int sms, cudaStream_t stream, bool resetOverflow);
 int pipeline_launch_count();
 
-void upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream);
-cudaError_t launch_simulate(const LaunchParams& p, bool trace, int ctas, unsigned long long* nextCand, cudaStream_t stream);
-int simulate_max_ctas(int device);
+void upload_constants(cudaStream_t stream);   // physics constants only (identical for every engine)
+cudaError_t launch_trace(const LaunchParams& p, cudaStream_t stream);
 
 // top-k selection on (cost, candidate id) among VALID candidates; see bcu_topk.cu
 cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCand, int64_t firstCandidate, int k,

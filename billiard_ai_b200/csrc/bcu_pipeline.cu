@@ -37,8 +37,6 @@ namespace bcu {
 
 namespace {
 
-__constant__ TableGeom p_table;
-__constant__ RulesData p_rules;
 __constant__ PhysConst p_phys;
 
 constexpr int ROUNDS = MAX_EVENTS + 1;  // round r applies event r+1; round MAX_EVENTS only flags overflow
@@ -163,7 +161,7 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
                 if (type >= 0) {
                     const float2 q = reinterpret_cast<const float2*>(p.states.pos)[(int64_t)c.sIdx * NB + b];
                     pos = mk(q.x, q.y);
-                    if (type == p_rules.cueType) {
+                    if (type == p.rules->cueType) {
                         vel = mk(c.vx, c.vy);
                         kind = K_SHOT;
                         nextRolling = time_to_rolling(vel, pc);  // type.cpp:502-506
@@ -327,7 +325,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
                 if (evType == E_POTTING) {                 // :1716-1746
                     A.vel = mk(0.f, 0.f); A.rolling = false; A.kind = K_POTTING;
                 } else if (evType == E_RAIL_COLLISION) {   // :1748-1786
-                    const RailGeom& rg = p_table.rails[evPartner];
+                    const RailGeom& rg = p.table->rails[evPartner];
                     A.vel = rail_collision(nvel, mk(rg.nx, rg.ny), pc);
                     A.rolling = true; A.kind = K_RAIL; cause = evPartner;
                 } else if (evType == E_REST) {             // :1788-1808
@@ -446,7 +444,7 @@ __global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restr
             q = w.pos[(int64_t)lane * w.n + s];
         }
         const unsigned pottedMask = __ballot_sync(FULL, kind == K_POTTING);
-        const unsigned cuePotted = __ballot_sync(FULL, kind == K_POTTING && type == p_rules.cueType);
+        const unsigned cuePotted = __ballot_sync(FULL, kind == K_POTTING && type == p.rules->cueType);
         const uint32_t expected = p.states.expectedMask[c.sIdx];
         const unsigned unexpected = __ballot_sync(FULL, kind == K_POTTING && !((expected >> (type & 31)) & 1u));
         uint64_t cost = ~0ull;
@@ -455,7 +453,7 @@ __global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restr
             double pottingScore = 0.0;
             for (unsigned m = pottedMask; m; m &= m - 1) {   // ascending ball index, as the oracle sums
                 const int b = __ffs(m) - 1;
-                pottingScore += p_rules.score[__shfl_sync(FULL, type, b)];
+                pottingScore += p.rules->score[__shfl_sync(FULL, type, b)];
             }
             const v2 v0 = mk(c.vx, c.vy);
             const float velocitySquared = dot(v0, v0);
@@ -485,7 +483,7 @@ __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspa
     for (int r = 0; r < ROUNDS; ++r) {
         const unsigned long long d = w.counts[4 * r + 1];
         if (w.counts[4 * r + 0] == 0) continue;
-        pairs += d * p.states.nBalls; rails += d * p_table.nRails; pockets += d * p_table.nPockets;
+        pairs += d * p.states.nBalls; rails += d * p.table->nRails; pockets += d * p.table->nPockets;
         quartics += w.counts[4 * r + 2];
     }
     atomicAdd(&p.out.counters[1], pairs); atomicAdd(&p.out.counters[2], quartics);
@@ -494,16 +492,11 @@ __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspa
 
 }  // namespace
 
-static int g_nRails = MAX_RAILS, g_nPockets = MAX_POCKETS;
-
-void pipeline_upload_constants(const TableGeom& table, const RulesData& rules, cudaStream_t stream) {
+void pipeline_upload_constants(cudaStream_t stream) {
     PhysConst pc = phys_const();
-    g_nRails = table.nRails; g_nPockets = table.nPockets;
+    cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
     cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(ITEM_BLOCK * (MAX_RAILS + MAX_POCKETS + 2 * MAX_BALLS) * sizeof(uint16_t)));
-    cudaMemcpyToSymbolAsync(p_table, &table, sizeof(TableGeom), 0, cudaMemcpyHostToDevice, stream);
-    cudaMemcpyToSymbolAsync(p_rules, &rules, sizeof(RulesData), 0, cudaMemcpyHostToDevice, stream);
-    cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
 }
 
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w) { return w.counts + 4 * ROUNDS + 3; }
@@ -549,15 +542,15 @@ int pipeline_launch_count() { return 2 + 3 * ROUNDS; }
 // One launch of the batch path over p->nCand <= w.n strikes.  `p` is a DEVICE pointer (the kernels read their parameters
 // from memory, so a captured CUDA graph of this sequence stays valid from call to call); all grids are persistent and
 // sized by the workspace capacity, so nothing in the launch sequence depends on the candidate count.
-cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, bool withCounters, const PipeWorkspace& wsIn, int sms,
-                            cudaStream_t stream, bool resetOverflow) {
+cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int nPockets, bool withCounters,
+                            const PipeWorkspace& wsIn, int sms, cudaStream_t stream, bool resetOverflow) {
     PipeWorkspace w = wsIn;
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
     const size_t countWords = (size_t)4 * (ROUNDS + 1) - (resetOverflow ? 0 : 1);
     if ((e = cudaMemsetAsync(w.counts, 0, countWords * sizeof(uint32_t), stream)) != cudaSuccess) return e;
-    const size_t itemSmem = (size_t)ITEM_BLOCK * (g_nRails + g_nPockets + 2 * nBalls) * sizeof(uint16_t);
+    const size_t itemSmem = (size_t)ITEM_BLOCK * (nRails + nPockets + 2 * nBalls) * sizeof(uint16_t);
     const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
     // BCU_ROUND_TIMING=1 (diagnosis only): CUDA events around every kernel, per-round times on stderr
     static const bool timing = getenv("BCU_ROUND_TIMING") != nullptr;

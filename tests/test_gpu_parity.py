@@ -322,3 +322,72 @@ def test_cpp_host_mirror_returns_the_reference_system(ref):
         assert bad == 0
         total_compared += compared.value
     assert total_compared > 350
+
+
+def _fresh_engine(table, **env):
+    """An engine created under the given BCU_* environment (the knobs are read by bcu_create)."""
+    from billiard_ai_b200 import Engine
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update({k: str(v) for k, v in env.items()})
+    try:
+        return Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+RESULT_KEYS = ("cost", "flags", "potted", "n_events", "final_time", "final_pos")
+
+
+def test_pipeline_knobs_do_not_change_results(engine, table):
+    """The batch pipeline cuts a launch into parts on concurrent streams, captures it in a CUDA graph and sizes its
+    quartic job queue for the common case (the host doubles it and re-runs the launch when a round overflows it).
+    None of that may change a bit of the results: one stream / no graph / a one-job-per-strike queue (which overflows
+    and is grown several times) against the default engine, event logs included."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.snooker22_open()
+    dirs, speeds = W.grid(256, 32)
+    vx, vy = W.grid_velocities(dirs, speeds)
+    engine.set_states(pos, types, 1 << 1)
+    want = engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True)
+    for env in ({"BCU_STREAMS": 1}, {"BCU_STREAMS": 3, "BCU_NO_GRAPH": 1}, {"BCU_JOBS_PER_STRIKE": 1}):
+        e = _fresh_engine(table, **env)
+        try:
+            e.set_states(pos, types, 1 << 1)
+            got = e.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True)
+            for key in RESULT_KEYS + ("event_log",):
+                assert np.array_equal(got[key], want[key]), (env, key)
+            again = e.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True, reuse_buffers=True)
+            for key in RESULT_KEYS + ("event_log",):   # page-locked, reused result buffers hold the same values
+                assert np.array_equal(again[key], want[key]), (env, "pinned", key)
+        finally:
+            e.close()
+
+
+def test_launch_larger_than_one_pipeline_pass(engine):
+    """More candidates than one pass takes (4 streams x 2^20 strikes): the launch is processed in several waves over the
+    same workspace.  Every candidate must come out exactly as when its shard of the grid is evaluated on its own."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.random_layout(6, 5)
+    dirs, speeds = W.grid(8192, 64)
+    ns = 9                                       # 9 x 8192 x 64 = 4 718 592 candidates > 4 x 2^20
+    spos = np.stack([np.roll(pos, i, axis=0) for i in range(ns)])
+    stypes = np.stack([types] * ns)
+    stypes[:, :] = 1
+    for i in range(ns):
+        stypes[i, i % 6] = 0                     # the cue ball sits somewhere else in every state
+    engine.set_states(spos, stypes, 1 << 1)
+    total = engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    assert total == ns * 8192 * 64
+    rng = np.random.RandomState(3)
+    windows = [(0, 4096), (2**20 - 2048, 4096), (4 * 2**20 - 1000, 3000), (total - 5000, 5000)]
+    windows += [(int(o), 2048) for o in rng.randint(0, total - 2048, 4)]
+    full = {off: engine.fetch(off, n) for off, n in windows}
+    for off, n in windows:
+        engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=off, count=n)
+        part = engine.fetch()
+        for key in RESULT_KEYS:
+            assert np.array_equal(part[key], full[off][key]), (off, key)
