@@ -37,10 +37,10 @@ struct DevBuf {
 }  // namespace
 
 struct PipeGraphKey {   // everything the captured launch sequence depends on
-    void* ws; void* params; int64_t per; int G; int nBalls; int jobsPerStrike; bool counters;
+    void* ws; void* params; int64_t per; int G; int nBalls; int jobsPerStrike; bool counters; int pruneMode;
     bool operator==(const PipeGraphKey& o) const {
         return ws == o.ws && params == o.params && per == o.per && G == o.G && nBalls == o.nBalls &&
-               jobsPerStrike == o.jobsPerStrike && counters == o.counters;
+               jobsPerStrike == o.jobsPerStrike && counters == o.counters && pruneMode == o.pruneMode;
     }
 };
 
@@ -80,6 +80,7 @@ struct bcu_engine {
     DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
     int sms = 148;
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
+    int pruneMode = 1;                  // reach bound on ball pairs (bcu_set_prune): 0 off, 1 on, 2 audit
     uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
     int pipeStreams = 4;             // BCU_STREAMS: parts of a launch in flight at once
     cudaStream_t pipeStream[PIPE_MAX_STREAMS] = {};
@@ -248,6 +249,10 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
         const int v = atoi(jv);
         e->jobsPerStrike = v < 1 ? 1 : v > 1024 ? 1024 : v;
     }
+    if (const char* pv = getenv("BCU_PRUNE")) {
+        const int v = atoi(pv);
+        e->pruneMode = v < 0 ? 0 : v > 2 ? 2 : v;
+    }
     if (const char* sv = getenv("BCU_STREAMS")) {
         const int v = atoi(sv);
         e->pipeStreams = v < 1 ? 1 : v > PIPE_MAX_STREAMS ? PIPE_MAX_STREAMS : v;
@@ -412,7 +417,7 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
                     const int64_t cnt = p.nCand - off < (int64_t)G * per ? p.nCand - off : (int64_t)G * per;
                     CK(cudaMemsetAsync(p.out.eventLog + (size_t)off * 32, 0xff, (size_t)cnt * 32 * sizeof(int4), e->stream));
                 }
-                PipeGraphKey key{e->dPipeWs.p, e->dPipeParams.p, per, G, nBalls, e->jobsPerStrike, withCounters};
+                PipeGraphKey key{e->dPipeWs.p, e->dPipeParams.p, per, G, nBalls, e->jobsPerStrike, withCounters, e->pruneMode};
                 const bool useGraph = e->useGraph;
                 if (!useGraph || !e->pipeGraph || !(key == e->pipeKey)) {
                     if (e->pipeGraph) { cudaGraphExecDestroy(e->pipeGraph); e->pipeGraph = nullptr; }
@@ -422,6 +427,7 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
                         PipeWorkspace ws{};
                         ws.base = e->dPipeWs.p + wsBytes * g;
                         pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, &ws);
+                        ws.pruneMode = e->pruneMode;
                         CK(cudaStreamWaitEvent(e->pipeStream[g], e->pipeFork, 0));
                         CK(launch_pipeline(e->dPipeParams.p + g, nBalls, e->table.nRails, e->table.nPockets, withCounters, ws, e->sms, e->pipeStream[g], true));
                         // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
@@ -793,6 +799,22 @@ int bcu_enable_counters(bcu_engine* e, int enable) {
     if (!e) return BCU_ERR_INVALID;
     e->countersOn = enable != 0;
     if (e->haveLast) e->last.out.counters = e->countersOn ? e->dCounters.p : nullptr;
+    return BCU_OK;
+}
+
+int bcu_set_prune(bcu_engine* e, int mode) {
+    if (!e || mode < 0 || mode > 2) return BCU_ERR_INVALID;
+    e->pruneMode = mode;
+    return BCU_OK;
+}
+
+int bcu_get_prune_counters(bcu_engine* e, uint64_t* out2) {
+    if (!e || !out2) return BCU_ERR_INVALID;
+    if (!e->dCounters.p) return fail(e, BCU_ERR_STATE, "bcu_get_prune_counters: no launch yet");
+    unsigned long long h[8];
+    CK(cudaMemcpyAsync(h, e->dCounters.p, sizeof(h), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    out2[0] = h[5]; out2[1] = h[6];
     return BCU_OK;
 }
 

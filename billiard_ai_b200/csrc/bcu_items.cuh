@@ -17,7 +17,7 @@
 constexpr int ITEM_BLOCK = 128;
 
 struct ItemCounts {
-    int rails, pockets, pairs, dynPairs;
+    int pairs, dynPairs;
 };
 
 // Appends the set bits of `mask` (as base | bit index) to a shared-memory queue; all 32 lanes must call.
@@ -44,11 +44,57 @@ __device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint16_t
     }
 }
 
+// ---- the reach bound --------------------------------------------------------------------------------------------------
+// A ball-pair quartic is only worth solving if its result could still beat the strike's best event time so far.  The
+// quartic of physics::timeToCollision (:326-337) is  |dP + dV t + dA t^2 / 2|^2 - d^2  with coefficients quantised to
+// 1e-6; the reference accepts a computed root x + iy as the collision time when |y| < 1e-3 (realRoot :550-560) and takes
+// the smallest such x, or none if that one is negative.  For any such root of the polynomial with 0 <= x <= T:
+//
+//     |dP| <= d + disp1(T) + disp2(T) + 1e-3 (|v1| + |v2| + (|a1| + |a2|) T) + q(T)
+//
+// where disp(T) = max(|v| T, |a| T^2 / 2) bounds |v t + a t^2 / 2| on [0, T] for an acceleration anti-parallel to the
+// velocity (the polynomial keeps decelerating past the stop, so the ball "comes back"), the third term is the change of
+// the polynomial over the 1e-3 imaginary strip, and q(T) = 0.05 mm (1 + T + T^2 + T^3 + T^4) covers the quantisation and
+// binary32 rounding of the coefficients.  A pair whose distance exceeds this REACH for T = (best time so far) cannot
+// produce the winning event -- PROVIDED the closed-form solver returns the polynomial's roots.  It does not always: when
+// the relative motion runs along a line (every moving-vs-resting pair: dA || dV) the depressed quartic is biquadratic up to
+// quantisation noise, Ferrari's S is then ~0 unless all four roots are real, and q/S is rounding noise that the reference
+// turns into an "event" about once in 5e5 such pairs.  Those results are reproduced bit for bit by solving the quartic;
+// the bound is only applied where the solver is well conditioned:
+//   * moving vs resting: only if the ball's polynomial passes the partner completely before its turning point
+//     (|dP| + d + 5 mm <= 0.99 v^2 / 2|a|: four real roots, S = half the sum of the two larger ones),
+//   * moving vs moving: only if the leading coefficient is >= 4e-3 (not nearly cubic) and the angle between dA and dV is
+//     >= 5.7 degrees (sin^2 >= 1e-2: not nearly collinear).
+// On top of the bound 2 ms and 2 mm of slack are left for the rounding of the solver in these regimes.  The strike's key
+// only decreases during a round, so any value read from it is a valid T.  mode 2 (audit) posts everything and marks the
+// jobs the bound would have skipped; quartic_kernel then counts the marked jobs whose result would have mattered
+// (tools/prune_audit.py, tests/test_gpu_parity.py).
+struct Reach {
+    float t;       // T + slack, seconds (NaN: no bound)
+    float fixed;   // d + 2 mm + q(t)
+};
+__device__ __forceinline__ Reach reach_of(float T, float diameter) {
+    Reach r;
+    r.t = T + 2e-3f;
+    const float poly = (((r.t + 1.0f) * r.t + 1.0f) * r.t + 1.0f) * r.t + 1.0f;
+    r.fixed = diameter + 2.0f + 0.05f * poly;
+    return r;
+}
+// reach contribution of one ball with speed v and deceleration a (both >= 0)
+__device__ __forceinline__ float reach_ball(const Reach& r, float v, float a) {
+    const float lin = v * r.t, quad = 0.5f * a * r.t * r.t;
+    return (lin > quad ? lin : quad) + 1e-3f * (v + a * r.t);
+}
+constexpr float PRUNE_MIN_LEADING = 4e-3f;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
+constexpr float PRUNE_MIN_SIN_SQ = 1e-2f;
+constexpr uint32_t JOB_MARK = 0x80000000u;   // audit: the bound would have skipped this job
+
 __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
     const LaunchParams& p = *pp;
     extern __shared__ uint16_t smemQ[];
     __shared__ ItemCounts cnt;
     __shared__ uint32_t sEnt[ITEM_BLOCK];
+    __shared__ float sT[ITEM_BLOCK];
     __shared__ uint32_t sJobBase;
     __shared__ RailGeom sRails[MAX_RAILS];
     __shared__ float sDetQV[MAX_RAILS];
@@ -64,9 +110,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
         sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
     }
     for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p.table->pockets[i];
-    uint16_t* qRails = smemQ;
-    uint16_t* qPockets = qRails + ITEM_BLOCK * R;
-    uint16_t* qPairs = qPockets + ITEM_BLOCK * P;
+    uint16_t* qPairs = smemQ;
     uint16_t* qDyn = qPairs + ITEM_BLOCK * NB;
     const int64_t n = w.n;
     const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
@@ -74,25 +118,30 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
     uint32_t* jobCount = &w.counts[4 * round + 2];
     const float diameter = p.table->diameter;
     const float dd = diameter * diameter;
+    const int prune = w.pruneMode;
+    unsigned long long skipped = 0;   // counters / audit only
 
     for (uint32_t base = blockIdx.x * ITEM_BLOCK; base < nDyn; base += gridDim.x * ITEM_BLOCK) {
-        if (tid == 0) { cnt.rails = 0; cnt.pockets = 0; cnt.pairs = 0; cnt.dynPairs = 0; }
+        if (tid == 0) { cnt.pairs = 0; cnt.dynPairs = 0; }
         __syncthreads();
 
         // ---- stage 1: this thread's ball against every rail, pocket and resting ball ---------------------------------
-        uint32_t railMask = 0, pocketMask = 0, statMask = 0, dynPairMask = 0, ent = 0;
+        uint32_t statMask = 0, statMarked = 0, dynPairMask = 0, ent = 0;
+        float tBest = __int_as_float(0x7fc00000);
         const uint32_t e = base + tid;
         if (e < nDyn) {
             ent = dyn[e];
             const int64_t s = ent >> 5;
             const int b = (int)(ent & 31u);
             const int64_t g = (int64_t)b * n + s;
-            const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g];
+            const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g], q3 = w.acc[g];
             const int lastRail = meta_last_rail(w.meta[g]);
             const uint32_t restMask = w.restMask[s], dynMask = w.dynMask[s];
-            const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y), dn = mk(q2n.x, q2n.y);
+            unsigned long long keyNow = __ldcg(key + s);   // rest / rolling offers of the strike (and whatever else is in)
+            const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y), dn = mk(q2n.x, q2n.y), acc = mk(q3.x, q3.y);
             dynPairMask = dynMask & ~((2u << b) - 1u);   // dynamic partners o > b (one job covers both orders)
             if (!is_zero(vel)) {
+                uint32_t railMask = 0, pocketMask = 0;
                 for (int r = 0; r < R; ++r) {
                     const RailGeom rg = sRails[r];
                     const float detDV = vel.x * rg.dy - vel.y * rg.dx;
@@ -113,22 +162,73 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
                     if (!(disc < 0)) pocketMask |= 1u << k;
                 }
                 const float len1 = length(vel);
+                const float accLen = length(acc);
+                // second stages of this ball's rails and pockets (a handful per ball): the quadratics of
+                // timeToCollisionWithRail (:181-238) and timeToTarget (:383-457); the earliest goes to the strike's key
+                unsigned long long best = ~0ull;
+                while (railMask) {
+                    const int r = __ffs(railMask) - 1;
+                    railMask &= railMask - 1;
+                    const RailGeom rg = sRails[r];
+                    const float detDV = vel.x * rg.dy - vel.y * rg.dx;
+                    const float detVP = rg.dx * pos.y - rg.dy * pos.x;
+                    const float lambda = (detVP + sDetQV[r]) / detDV;   // recomputed exactly as the first stage did
+                    const float distance = length(lambda * vel);
+                    float x[2];
+                    if (solve_quadratic(0.5f * -accLen, len1, -distance, x) != 0 && x[0] == x[0]) {
+                        const unsigned long long k2 = ((unsigned long long)ordered_bits(x[0]) << 32) | make_code(b, CAT_RAIL, r);
+                        best = k2 < best ? k2 : best;
+                    }
+                }
+                while (pocketMask) {
+                    const int k = __ffs(pocketMask) - 1;
+                    pocketMask &= pocketMask - 1;
+                    float t;
+                    if (time_to_pocket(sPockets[k], pos, dn, vel, acc, &t) && t == t) {
+                        const unsigned long long k2 = ((unsigned long long)ordered_bits(t) << 32) | make_code(b, CAT_POCKET, k);
+                        best = k2 < best ? k2 : best;
+                    }
+                }
+                if (best != ~0ull) atomicMin(key + s, best);
+                keyNow = best < keyNow ? best : keyNow;
+                tBest = from_ordered_bits((uint32_t)(keyNow >> 32));   // NaN when the strike has no offer at all
+                const Reach rc = reach_of(tBest, diameter);
+                const float reach = rc.fixed + reach_ball(rc, len1, accLen);
+                const float reachSq = reach * reach;
+                // resting partners this far at most are passed completely before the turning point (see above)
+                const float passMax = 0.99f * (len1 * len1) / (2.0f * accLen) - diameter - 5.0f;
+                const float passMaxSq = passMax > 0.0f ? passMax * passMax : -1.0f;
                 const float2* posOf = w.pos + s;
-                for (int o = 0; o < NB; ++o) {
-                    if (!((restMask >> o) & 1u)) continue;
-                    const float2 q2 = posOf[(int64_t)o * n];
-                    const v2 toPoint = mk(q2.x, q2.y) - pos;
-                    const float factor = dot(dn, toPoint) / len1;
-                    const v2 dv = toPoint - (vel * factor);
-                    const float dist = factor < 0 ? dot(toPoint, toPoint) : dot(dv, dv);
-                    if (!(dist > dd)) statMask |= 1u << o;
+                for (int o0 = 0; o0 < NB; o0 += 8) {
+                    float2 qq[8];
+                    #pragma unroll
+                    for (int k = 0; k < 8; ++k)   // independent loads first: one memory round trip per 8 partners
+                        qq[k] = (o0 + k < NB && ((restMask >> (o0 + k)) & 1u)) ? posOf[(int64_t)(o0 + k) * n] : make_float2(0.f, 0.f);
+                    #pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int o = o0 + k;
+                        if (o >= NB || !((restMask >> o) & 1u)) continue;
+                        const v2 toPoint = mk(qq[k].x, qq[k].y) - pos;
+                        const float factor = dot(dn, toPoint) / len1;
+                        const v2 dv = toPoint - (vel * factor);
+                        const float distSq = dot(toPoint, toPoint);
+                        const float dist = factor < 0 ? distSq : dot(dv, dv);
+                        if (!(dist > dd)) {
+                            if (prune && distSq > reachSq && distSq <= passMaxSq) {
+                                ++skipped;
+                                if (prune == 2) { statMask |= 1u << o; statMarked |= 1u << o; }
+                            } else {
+                                statMask |= 1u << o;
+                            }
+                        }
+                    }
                 }
             }
         }
         sEnt[tid] = ent;
-        push_mask(railMask, (uint32_t)tid << 5, qRails, &cnt.rails);
-        push_mask(pocketMask, (uint32_t)tid << 5, qPockets, &cnt.pockets);
-        push_mask(statMask, (uint32_t)tid << 6, qPairs, &cnt.pairs);
+        sT[tid] = tBest;
+        push_mask(statMask & ~statMarked, (uint32_t)tid << 6, qPairs, &cnt.pairs);
+        if (prune == 2) push_mask(statMarked, ((uint32_t)tid << 6) | 0x8000u, qPairs, &cnt.pairs);
         push_mask(dynPairMask, (uint32_t)tid << 5, qDyn, &cnt.dynPairs);
         __syncthreads();
 
@@ -145,6 +245,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
                     const int o = (int)(c2 & 31u), b = (int)(en & 31u);
                     const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
                     const float2 x1 = w.pos[g1], y1 = w.vel[g1], n1 = w.vn[g1], x2 = w.pos[g2], y2 = w.vel[g2], n2 = w.vn[g2];
+                    const float2 z1 = w.acc[g1], z2 = w.acc[g2];
                     const v2 p1 = mk(x1.x, x1.y), v1 = mk(y1.x, y1.y), p2 = mk(x2.x, x2.y), w2 = mk(y2.x, y2.y);
                     const v2 v1n = mk(n1.x, n1.y), w2n = mk(n2.x, n2.y);
                     // the reference tests b -> o and, on o's own turn, o -> b; the quantised coefficients of both
@@ -158,6 +259,18 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
                         else pass = !(point_to_half_line_sq(pa, va, pb) > diameter * diameter);   // :318-324
                     }
                     code = ((c2 >> 5) << 6) | 32u | (uint32_t)o;
+                    if (pass && prune) {
+                        const Reach rc = reach_of(sT[c2 >> 5], diameter);
+                        const v2 a1 = mk(z1.x, z1.y), a2 = mk(z2.x, z2.y);
+                        const float reach = rc.fixed + reach_ball(rc, length(v1), length(a1)) + reach_ball(rc, length(w2), length(a2));
+                        const v2 dA = (a1 - a2) * (1.0f / 1000.0f), dV = (v1 - w2) * (1.0f / 1000.0f), dP = p2 - p1;
+                        const float aa = dot(dA, dA), vv = dot(dV, dV), cr = dA.x * dV.y - dA.y * dV.x;
+                        if (0.25f * aa >= PRUNE_MIN_LEADING && vv > 0.0f && cr * cr >= PRUNE_MIN_SIN_SQ * (aa * vv) && !is_zero(v1) && !is_zero(w2) &&
+                            dot(dP, dP) > reach * reach) {
+                            ++skipped;
+                            if (prune == 2) code |= 0x8000u; else pass = false;
+                        }
+                    }
                 }
                 const unsigned m = __ballot_sync(FULL, pass);
                 if (m) {
@@ -170,63 +283,31 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
         }
         __syncthreads();
 
-        // ---- stage 2: one survivor per thread over the concatenated queues [rails | pockets | pairs] -------------------
+        // ---- stage 2: quantised coefficients of the surviving pairs, one per thread -> global job queue -------------------
         {
-            const int cR = cnt.rails, cP = cnt.pockets, cQ = cnt.pairs;
-            const int totalQ = cR + cP + cQ;
+            const int cQ = cnt.pairs;
             if (tid == 0 && cQ > 0) sJobBase = atomicAdd(jobCount, (uint32_t)cQ);   // one global atomic per tile
             __syncthreads();
-            for (int i0 = 0; i0 < totalQ; i0 += ITEM_BLOCK) {
-                const int i = i0 + tid;
-                const bool isRail = i < cR, isPocket = !isRail && i < cR + cP, isPair = !isRail && !isPocket && i < totalQ;
-                if (isRail) {
-                    const uint32_t c2 = qRails[i];
-                    const uint32_t en = sEnt[c2 >> 5];
-                    const int r = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5, g = (int64_t)b * n + s;
-                    const float2 q0 = w.pos[g], q1 = w.vel[g], q3 = w.acc[g];
-                    const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y);
-                    const RailGeom rg = sRails[r];
-                    // lambda of halfLineIntersectsLineSegment, recomputed exactly as stage 1 did
-                    const float detDV = vel.x * rg.dy - vel.y * rg.dx;
-                    const float detVP = rg.dx * pos.y - rg.dy * pos.x;
-                    const float lambda = (detVP + sDetQV[r]) / detDV;
-                    const float distance = length(lambda * vel);
-                    const float velocity = length(vel);
-                    const float a = -length(mk(q3.x, q3.y));
-                    float x[2];
-                    if (solve_quadratic(0.5f * a, velocity, -distance, x) != 0) offer(key + s, x[0], make_code(b, CAT_RAIL, r));
-                } else if (isPocket) {
-                    const uint32_t c2 = qPockets[i - cR];
-                    const uint32_t en = sEnt[c2 >> 5];
-                    const int k = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5, g = (int64_t)b * n + s;
-                    const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g], q3 = w.acc[g];
-                    float t;
-                    if (time_to_pocket(sPockets[k], mk(q0.x, q0.y), mk(q2n.x, q2n.y), mk(q1.x, q1.y), mk(q3.x, q3.y), &t))
-                        offer(key + s, t, make_code(b, CAT_POCKET, k));
-                }
-                else if (isPair) {   // quantised coefficients -> global job queue
-                    const int iq = i - cR - cP;
-                    const uint32_t c2 = qPairs[iq];
-                    const uint32_t en = sEnt[c2 >> 6];
-                    const int o = (int)(c2 & 31u), b = (int)(en & 31u);
-                    const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
-                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2], y2 = w.vel[g2], z2 = w.acc[g2];
-                    float co[5];
-                    collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), mk(z2.x, z2.y), mk(y2.x, y2.y),
-                                           mk(x2.x, x2.y), diameter, co);
-                    const uint64_t j = (uint64_t)sJobBase + iq;
-                    if (j < w.jobCap) {
-                        #pragma unroll
-                        for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
-                        w.jobCode[j] = (en << 6) | (c2 & 63u);
-                    } else {
-                        w.counts[4 * ROUNDS + 3] = 1u;  // queue overflow: the host grows the queue and re-runs the launch
-                    }
+            for (int iq = tid; iq < cQ; iq += ITEM_BLOCK) {
+                const uint32_t c2 = qPairs[iq];
+                const uint32_t en = sEnt[(c2 >> 6) & (ITEM_BLOCK - 1)];
+                const int o = (int)(c2 & 31u), b = (int)(en & 31u);
+                const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
+                const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2], y2 = w.vel[g2], z2 = w.acc[g2];
+                float co[5];
+                collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), mk(z2.x, z2.y), mk(y2.x, y2.y),
+                                       mk(x2.x, x2.y), diameter, co);
+                const uint64_t j = (uint64_t)sJobBase + iq;
+                if (j < w.jobCap) {
+                    #pragma unroll
+                    for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
+                    w.jobCode[j] = (en << 6) | (c2 & 63u) | ((c2 & 0x8000u) ? JOB_MARK : 0u);
+                } else {
+                    w.counts[4 * ROUNDS + 3] = 1u;  // queue overflow: the host grows the queue and re-runs the launch
                 }
             }
         }
         __syncthreads();
     }
+    if (p.out.counters && skipped) atomicAdd(&p.out.counters[5], skipped);
 }

@@ -78,10 +78,11 @@ struct PipeWorkspace {
     // stream-compacted lists, by round & 1
     uint32_t* live;            // [2][n] strike ids
     uint32_t* dyn;             // [2][dynCap] strike << 5 | ball
-    uint32_t* counts;          // [rounds + 1][4] {live, dynamic balls, quartic jobs, -}
+    uint32_t* counts;          // [rounds + 1][4] {live, dynamic balls, quartic jobs, -}; last row: {-, -, audit failures, queue overflow}
     // quartic jobs of the round
     float* jobCo;              // [5][jobCap]
-    uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner
+    uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner; bit 31 = audit mark
+    int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
 };
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);

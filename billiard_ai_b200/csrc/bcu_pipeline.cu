@@ -217,7 +217,13 @@ __global__ void __launch_bounds__(QUARTIC_BLOCK) quartic_kernel(PipeWorkspace w,
         const uint32_t c2 = w.jobCode[j];
         float t;
         if (collision_time_from_coefficients(co, &t)) {
-            const uint32_t ent = c2 >> 6;
+            const uint32_t ent = (c2 & ~JOB_MARK) >> 6;
+            if (c2 & JOB_MARK) {
+                // audit (pruneMode 2): the reach bound would have skipped this job, so its time must lose against the
+                // strike's best so far (which only decreases); anything else is a failure of the bound
+                const float tNow = from_ordered_bits((uint32_t)(__ldcg(key + (ent >> 5)) >> 32));
+                if (!(t > tNow)) atomicAdd(&w.counts[4 * ROUNDS + 2], 1u);
+            }
             offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
         }
     }
@@ -475,7 +481,8 @@ __global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restr
     if (p.out.counters && lane == 0 && events) atomicAdd(&p.out.counters[0], events);
 }
 
-// work counters from the per-round list sizes: [1] pair items [2] quartics [3] rail items [4] pocket items
+// work counters from the per-round list sizes: [1] pair items [2] quartics solved [3] rail items [4] pocket items
+// [5] pairs the reach bound skipped (or, in audit mode, marked)  [6] audit: marked jobs that would have mattered
 __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
     const LaunchParams& p = *pp;
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -488,6 +495,7 @@ __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspa
     }
     atomicAdd(&p.out.counters[1], pairs); atomicAdd(&p.out.counters[2], quartics);
     atomicAdd(&p.out.counters[3], rails); atomicAdd(&p.out.counters[4], pockets);
+    atomicAdd(&p.out.counters[6], (unsigned long long)w.counts[4 * ROUNDS + 2]);   // [5] (skipped pairs) is added by items_kernel
 }
 
 }  // namespace
@@ -495,8 +503,6 @@ __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspa
 void pipeline_upload_constants(cudaStream_t stream) {
     PhysConst pc = phys_const();
     cudaMemcpyToSymbolAsync(p_phys, &pc, sizeof(PhysConst), 0, cudaMemcpyHostToDevice, stream);
-    cudaFuncSetAttribute(items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)(ITEM_BLOCK * (MAX_RAILS + MAX_POCKETS + 2 * MAX_BALLS) * sizeof(uint16_t)));
 }
 
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w) { return w.counts + 4 * ROUNDS + 3; }
@@ -550,7 +556,8 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
     const size_t countWords = (size_t)4 * (ROUNDS + 1) - (resetOverflow ? 0 : 1);
     if ((e = cudaMemsetAsync(w.counts, 0, countWords * sizeof(uint32_t), stream)) != cudaSuccess) return e;
-    const size_t itemSmem = (size_t)ITEM_BLOCK * (nRails + nPockets + 2 * nBalls) * sizeof(uint16_t);
+    const size_t itemSmem = (size_t)ITEM_BLOCK * (2 * nBalls) * sizeof(uint16_t);
+    (void)nRails; (void)nPockets;
     const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
     // BCU_ROUND_TIMING=1 (diagnosis only): CUDA events around every kernel, per-round times on stderr
     static const bool timing = getenv("BCU_ROUND_TIMING") != nullptr;

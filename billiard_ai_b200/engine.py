@@ -344,5 +344,14 @@ class Engine:
         self._ck(self.lib.bcu_get_counters(self.h, _p(out, C.c_uint64)), "bcu_get_counters")
         return dict(zip(["events", "pair_items", "quartics", "rail_items", "pocket_items"], out.tolist()))
 
+    def set_prune(self, mode):
+        """0 off, 1 on (default), 2 audit; see include/billiard_cuda.h."""
+        self._ck(self.lib.bcu_set_prune(self.h, C.c_int(int(mode))), "bcu_set_prune")
+
+    def prune_counters(self):
+        out = np.zeros(2, np.uint64)
+        self._ck(self.lib.bcu_get_prune_counters(self.h, _p(out, C.c_uint64)), "bcu_get_prune_counters")
+        return dict(zip(["skipped", "audit_failures"], out.tolist()))
+
     def launch_count(self):
         return int(self.lib.bcu_launch_count(self.h))

@@ -169,6 +169,14 @@ int bcu_last_kernel_ms(bcu_engine* e, float* out_ms);
 /* work counters of the last launch when enabled: {events, pair items, quartics, rail items, pocket items} */
 int bcu_enable_counters(bcu_engine* e, int enable);
 int bcu_get_counters(bcu_engine* e, uint64_t* out5);
+/* Reach bound on ball pairs: a pair whose centre distance exceeds what the two balls can cover
+ * before the strike's best event time so far cannot produce the next event (the reference would solve its quartic,
+ * billiard_physics.cpp:283-381, and discard the result in min(), billiard_search.cpp:2002-2013), so it is not solved.
+ * mode 0: off (every quartic the reference solves is solved); 1: on (default); 2: audit -- everything is solved and the
+ * jobs the bound would have skipped are checked: out2 = {pairs skipped or marked, marked jobs whose result would have
+ * mattered}; the second number must be 0.  Counters need bcu_enable_counters(e, 1). */
+int bcu_set_prune(bcu_engine* e, int mode);
+int bcu_get_prune_counters(bcu_engine* e, uint64_t* out2);
 /* number of kernels launched by this engine so far */
 int64_t bcu_launch_count(const bcu_engine* e);
 
