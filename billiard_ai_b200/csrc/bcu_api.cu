@@ -82,7 +82,7 @@ struct bcu_engine {
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
     int pruneMode = 1;                  // reach bound on ball pairs (bcu_set_prune): 0 off, 1 on, 2 audit
     uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
-    int pipeStreams = 4;             // BCU_STREAMS: parts of a launch in flight at once
+    int pipeStreams = 2;             // BCU_STREAMS: parts of a launch in flight at once (measured: 2 best at 65 536 strikes)
     cudaStream_t pipeStream[PIPE_MAX_STREAMS] = {};
     cudaEvent_t pipeDone[PIPE_MAX_STREAMS] = {};
     cudaEvent_t pipeFork = nullptr;

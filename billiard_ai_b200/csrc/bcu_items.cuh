@@ -15,6 +15,9 @@
 #pragma once
 
 constexpr int ITEM_BLOCK = 128;
+#ifndef ITEM_MIN_BLOCKS
+#define ITEM_MIN_BLOCKS 6
+#endif
 
 struct ItemCounts {
     int pairs, dynPairs;
@@ -89,7 +92,7 @@ constexpr float PRUNE_MIN_LEADING = 4e-3f;   // m^2/s^4; moving-vs-resting pairs
 constexpr float PRUNE_MIN_SIN_SQ = 1e-2f;
 constexpr uint32_t JOB_MARK = 0x80000000u;   // audit: the bound would have skipped this job
 
-__global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+__global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
     const LaunchParams& p = *pp;
     extern __shared__ uint16_t smemQ[];
     __shared__ ItemCounts cnt;
@@ -101,15 +104,17 @@ __global__ void __launch_bounds__(ITEM_BLOCK) items_kernel(const LaunchParams* _
     __shared__ PocketGeom sPockets[MAX_POCKETS];
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
     const int R = p.table->nRails, P = p.table->nPockets, NB = p.states.nBalls;
-    const uint32_t nDyn = w.counts[4 * round + 1];
-    if (nDyn == 0) return;
     for (int i = tid; i < R; i += ITEM_BLOCK) {
         const RailGeom rg = p.table->rails[i];
         sRails[i] = rg;
         sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
     }
     for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p.table->pockets[i];
+    cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
+    const uint32_t nDyn = w.counts[4 * round + 1];
+    if (nDyn == 0) return;
     uint16_t* qPairs = smemQ;
     uint16_t* qDyn = qPairs + ITEM_BLOCK * NB;
     const int64_t n = w.n;

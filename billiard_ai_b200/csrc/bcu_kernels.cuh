@@ -82,6 +82,7 @@ struct PipeWorkspace {
     // quartic jobs of the round
     float* jobCo;              // [5][jobCap]
     uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner; bit 31 = audit mark
+    int pdlEarly;              // kernels signal cudaTriggerProgrammaticLaunchCompletion() at once (launch_pipeline)
     int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
 };
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);

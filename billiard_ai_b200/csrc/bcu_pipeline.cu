@@ -41,6 +41,9 @@ __constant__ PhysConst p_phys;
 
 constexpr int ROUNDS = MAX_EVENTS + 1;  // round r applies event r+1; round MAX_EVENTS only flags overflow
 constexpr int QUARTIC_BLOCK = 128;
+#ifndef QUARTIC_MIN_BLOCKS
+#define QUARTIC_MIN_BLOCKS 6
+#endif
 constexpr int APPLY_BLOCK = 256;
 
 enum Category : uint32_t { CAT_REST = 0, CAT_ROLLING = 1, CAT_STATIC_PAIR = 2, CAT_DYNAMIC_PAIR = 3, CAT_RAIL = 4, CAT_POCKET = 5 };
@@ -142,6 +145,7 @@ __device__ __forceinline__ void mark_finished(const LaunchParams& p, int64_t s, 
 // arrays are ball-major, [ball][strike], so consecutive threads write consecutive words).
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();   // see launch_pipeline
     const LaunchParams& p = *pp;
     __shared__ AppendShared ash;
     const int NB = p.states.nBalls;
@@ -206,7 +210,9 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 // ---------------------------------------------------------------------------------------------------------------------
 // quartic: one thread per job.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(QUARTIC_BLOCK) quartic_kernel(PipeWorkspace w, int round) {
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
     const uint32_t posted = w.counts[4 * round + 2];
     const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
     unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
@@ -275,10 +281,11 @@ __device__ __forceinline__ void offer_own(unsigned long long* key, const BallRec
 }
 
 __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
     const LaunchParams& p = *pp;
     __shared__ AppendShared ash;
-    const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
+    cudaGridDependencySynchronize();
     const uint32_t nLive = w.counts[4 * round + 0], nDyn = w.counts[4 * round + 1];
     if (nLive == 0) return;
     const uint32_t* live = w.live + (size_t)(round & 1) * w.n;
@@ -433,10 +440,12 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
 // rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
 // One warp per strike, lane = ball.
 __global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
     const LaunchParams& p = *pp;
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int NB = p.states.nBalls;
+    cudaGridDependencySynchronize();
     const int64_t warpsTotal = (int64_t)gridDim.x * (blockDim.x >> 5);
     unsigned long long events = 0;
     for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
@@ -578,18 +587,40 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if (occApply < 1) occApply = 1;
         occSmem = itemSmem;
     }
+    // Programmatic dependent launch: every kernel after init is launched with the stream-serialisation attribute and signals
+    // cudaTriggerProgrammaticLaunchCompletion() at once, so the CTAs of kernel k+1 are placed (and run their prologue: table
+    // geometry to shared memory) while kernel k drains; they read nothing kernel k writes before cudaGridDependencySynchronize().
+    // A round is three latency-bound kernels, so launch gaps are a visible share of a level.  BCU_NO_PDL=1 switches it off.
+    static const int pdlMode = getenv("BCU_PDL") ? atoi(getenv("BCU_PDL")) : 1;
+    const bool pdl = pdlMode > 0;
+    w.pdlEarly = pdlMode > 1;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    auto cfgOf = [&](unsigned grid, unsigned block, size_t smem) {
+        cudaLaunchConfig_t c{};
+        c.gridDim = dim3(grid); c.blockDim = dim3(block); c.dynamicSmemBytes = smem; c.stream = stream;
+        c.attrs = attr; c.numAttrs = pdl ? 1 : 0;
+        return c;
+    };
     mark();
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     mark();
     for (int r = 0; r < ROUNDS; ++r) {
-        items_kernel<<<sms * occItems, ITEM_BLOCK, itemSmem, stream>>>(p, w, r);
+        cudaLaunchConfig_t ci = cfgOf(sms * occItems, ITEM_BLOCK, itemSmem);
+        if ((e = cudaLaunchKernelEx(&ci, items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
-        quartic_kernel<<<sms * occQuartic, QUARTIC_BLOCK, 0, stream>>>(w, r);
+        cudaLaunchConfig_t cq = cfgOf(sms * occQuartic, QUARTIC_BLOCK, 0);
+        if ((e = cudaLaunchKernelEx(&cq, quartic_kernel, w, r)) != cudaSuccess) return e;
         mark();
-        apply_kernel<<<sms * occApply, APPLY_BLOCK, 0, stream>>>(p, w, r);
+        cudaLaunchConfig_t ca = cfgOf(sms * occApply, APPLY_BLOCK, 0);
+        if ((e = cudaLaunchKernelEx(&ca, apply_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
     }
-    finish_kernel<<<(unsigned)(finBlocks < sms * 8 ? finBlocks : sms * 8), 256, 0, stream>>>(p, w);
+    {
+        cudaLaunchConfig_t cf = cfgOf((unsigned)(finBlocks < sms * 8 ? finBlocks : sms * 8), 256, 0);
+        if ((e = cudaLaunchKernelEx(&cf, finish_kernel, p, w)) != cudaSuccess) return e;
+    }
     mark();
     if (timing) {
         cudaStreamSynchronize(stream);

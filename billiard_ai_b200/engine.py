@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libbilliard_cuda.so")
+LIB_PATH = os.environ.get("BCU_LIB") or os.path.join(HERE, "libbilliard_cuda.so")   # BCU_LIB: tuning builds (tools/build_variant.sh)
 
 F_COMPLETED, F_VALID, F_OVERFLOW, F_NOEVENT = 1, 2, 4, 8
 MAX_LAYERS = 32
