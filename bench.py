@@ -11,7 +11,8 @@ N > 1 -- merged across GPUs with one ncclAllGather of the per-GPU record blocks.
 
   value : whole-job strikes/s, inputs resident in HBM (CUDA events on the engine's stream, max over ranks)
   e2e   : the same level through the host-buffer C-ABI calls (bcu_set_states + bcu_evaluate + bcu_level_select +
-          bcu_fetch_beam): pinned host candidate arrays in, per-candidate results and the beam out, wall clock
+          bcu_fetch_beam): pinned host candidate arrays in; per-candidate cost / flags / potted mask / final time and the
+          beam (k best strikes with their final table positions) out, wall clock
   roofline     : the simulate kernel's algorithmic FP64 work / its CUDA-event time vs. the FP64 vector issue peak
                  measured in the same run (un-fused DADD+DMUL: FMA contraction is forbidden on this path)
   cpu_baseline : the reference's own CPU code (oracle/_ref/libref_oracle.so) on a bounded sample, all host threads
@@ -241,7 +242,7 @@ def run_b200(args, rank, local_rank, world):
 
     def e2e_step():
         eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"])
-        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=True, event_log=False, reuse_buffers=True)
+        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True)
         eng.level_select(BEAM)
         b = eng.fetch_beam()
         return res, b
@@ -260,7 +261,7 @@ def run_b200(args, rank, local_rank, world):
     assert np.array_equal(b2["cost"], beam["cost"]) and np.array_equal(b2["id"], beam["id"]), "e2e beam != resident beam"
     nb = len(types)
     h2d = mine * (4 + 4 + 4 + 8 + 8) + nb * (8 + 4) + 4
-    d2h = mine * (8 + 4 + 4 + 4 + nb * 8) + BEAM * (24 + nb * 8)
+    d2h = mine * (8 + 4 + 4 + 4) + BEAM * (24 + nb * 8)   # per-strike cost / flags / potted / time + the beam records
 
     if rank != 0:
         if world > 1:

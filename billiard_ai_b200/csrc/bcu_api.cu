@@ -492,7 +492,8 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n));
     CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
     const bool wantPos = out && out->final_pos, wantLog = out && out->event_log;
-    int rc = reserve_results(e, n, wantPos, wantLog);
+    // final positions are always produced on the device (the beam records need them); they are copied out on request
+    int rc = reserve_results(e, n, true, wantLog);
     if (rc) return rc;
     CK(cudaMemcpyAsync(e->dCandState.p, stateIdx, n * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dVx.p, vx, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
@@ -500,7 +501,8 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     CK(cudaMemcpyAsync(e->dSearchCost.p, searchCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dBaseCost.p, baseCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
     LaunchParams p;
-    fill_common(e, p, n, wantPos, wantLog);
+    fill_common(e, p, n, true, wantLog);
+    (void)wantPos;
     p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
     p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
     rc = run(e, p, false);

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
     __shared__ uint32_t sJobBase;
     __shared__ RailGeom sRails[MAX_RAILS];
     __shared__ float sDetQV[MAX_RAILS];
+    __shared__ float sRailLenSq[MAX_RAILS];   // |end - start|^2, or -1 when the component u is divided by is too short to filter on
     __shared__ PocketGeom sPockets[MAX_POCKETS];
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
@@ -110,6 +111,8 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
         const RailGeom rg = p.table->rails[i];
         sRails[i] = rg;
         sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
+        const float used = fabsf(rg.dx != 0.0f ? rg.dx : rg.dy);
+        sRailLenSq[i] = used >= 5.0f ? rg.dx * rg.dx + rg.dy * rg.dy : -1.0f;
     }
     for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p.table->pockets[i];
     cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
@@ -147,15 +150,27 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
             dynPairMask = dynMask & ~((2u << b) - 1u);   // dynamic partners o > b (one job covers both orders)
             if (!is_zero(vel)) {
                 uint32_t railMask = 0, pocketMask = 0;
+                // Rails, pass A (no division): which rails can the half-line cross at all?  The exact test below divides twice
+                // per rail; here a rail is dropped only when the exact test is certain to fail: the intersection parameter
+                // t = N / detDV is negative by more than any rounding (N detDV < 0, |t| > 1e-10), or -- for lines at more than
+                // ~1.1 degrees (sin^2 >= 4e-4), where both this estimate and the reference's u are accurate to < 1e-2 -- the
+                // crossing lies more than 5 % of the segment outside it.  Everything else is a candidate (prune mode 0: all).
+                const float speedSq = dot(vel, vel);
                 for (int r = 0; r < R; ++r) {
                     const RailGeom rg = sRails[r];
                     const float detDV = vel.x * rg.dy - vel.y * rg.dx;
-                    const float detVP = rg.dx * pos.y - rg.dy * pos.x;
-                    const float t = (detVP + sDetQV[r]) / detDV;
-                    const bool useX = rg.dx != 0.0f;
-                    const float num = useX ? (pos.x + t * vel.x - rg.sx) : (pos.y + t * vel.y - rg.sy);
-                    const float u = num / (useX ? rg.dx : rg.dy);
-                    if (r != lastRail && detDV != 0.0f && !(t < 0.0f) && !(u < 0.0f || u > 1.0f)) railMask |= 1u << r;
+                    const float nT = (rg.dx * pos.y - rg.dy * pos.x) + sDetQV[r];
+                    bool cand = r != lastRail && detDV != 0.0f;
+                    if (prune) {
+                        const bool behind = nT * detDV < 0.0f && fabsf(nT) > 1e-10f * fabsf(detDV);
+                        const float lenSq = sRailLenSq[r];
+                        const float nU = (pos.x - rg.sx) * vel.y - (pos.y - rg.sy) * vel.x;   // u = nU / -detDV
+                        const float den = -detDV, sgnU = den < 0.0f ? -nU : nU, aden = fabsf(den);
+                        const bool wellCond = lenSq > 0.0f && detDV * detDV >= 4e-4f * (speedSq * lenSq);
+                        const bool outside = wellCond && (sgnU < -0.05f * aden || sgnU > 1.05f * aden);
+                        cand = cand && !behind && !outside;
+                    }
+                    if (cand) railMask |= 1u << r;
                 }
                 for (int k = 0; k < P; ++k) {
                     const PocketGeom pg = sPockets[k];
@@ -175,9 +190,14 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
                     const int r = __ffs(railMask) - 1;
                     railMask &= railMask - 1;
                     const RailGeom rg = sRails[r];
+                    // halfLineIntersectsLineSegment (:725-753) via lineIntersectsLine (:651-723), exactly
                     const float detDV = vel.x * rg.dy - vel.y * rg.dx;
                     const float detVP = rg.dx * pos.y - rg.dy * pos.x;
-                    const float lambda = (detVP + sDetQV[r]) / detDV;   // recomputed exactly as the first stage did
+                    const float lambda = (detVP + sDetQV[r]) / detDV;
+                    const bool useX = rg.dx != 0.0f;
+                    const float num = useX ? (pos.x + lambda * vel.x - rg.sx) : (pos.y + lambda * vel.y - rg.sy);
+                    const float u = num / (useX ? rg.dx : rg.dy);
+                    if (lambda < 0.0f || u < 0.0f || u > 1.0f) continue;
                     const float distance = length(lambda * vel);
                     float x[2];
                     if (solve_quadratic(0.5f * -accLen, len1, -distance, x) != 0 && x[0] == x[0]) {
@@ -203,28 +223,42 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
                 // resting partners this far at most are passed completely before the turning point (see above)
                 const float passMax = 0.99f * (len1 * len1) / (2.0f * accLen) - diameter - 5.0f;
                 const float passMaxSq = passMax > 0.0f ? passMax * passMax : -1.0f;
+                // Resting partners, pass A (no division): a partner farther than d + 0.5 mm from the LINE of motion fails the
+                // reference's corridor test (:318-324) whichever arm it takes (the cross product with the stored unit velocity
+                // is the perpendicular distance to ~1e-3 mm); only the others get the exact test.  Prune mode 0: all of them.
                 const float2* posOf = w.pos + s;
+                uint32_t candMask = 0;
+                const float corridor = diameter + 0.5f;
                 for (int o0 = 0; o0 < NB; o0 += 8) {
                     float2 qq[8];
+                    const float2* src = posOf + (int64_t)o0 * n;
                     #pragma unroll
-                    for (int k = 0; k < 8; ++k)   // independent loads first: one memory round trip per 8 partners
-                        qq[k] = (o0 + k < NB && ((restMask >> (o0 + k)) & 1u)) ? posOf[(int64_t)(o0 + k) * n] : make_float2(0.f, 0.f);
+                    for (int k = 0; k < 8; ++k) {   // independent loads first: one memory round trip per 8 partners
+                        qq[k] = (o0 + k < NB && ((restMask >> (o0 + k)) & 1u)) ? *src : make_float2(0.f, 0.f);
+                        src += n;
+                    }
                     #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        const int o = o0 + k;
-                        if (o >= NB || !((restMask >> o) & 1u)) continue;
-                        const v2 toPoint = mk(qq[k].x, qq[k].y) - pos;
-                        const float factor = dot(dn, toPoint) / len1;
-                        const v2 dv = toPoint - (vel * factor);
-                        const float distSq = dot(toPoint, toPoint);
-                        const float dist = factor < 0 ? distSq : dot(dv, dv);
-                        if (!(dist > dd)) {
-                            if (prune && distSq > reachSq && distSq <= passMaxSq) {
-                                ++skipped;
-                                if (prune == 2) { statMask |= 1u << o; statMarked |= 1u << o; }
-                            } else {
-                                statMask |= 1u << o;
-                            }
+                        const float cr = dn.x * (qq[k].y - pos.y) - dn.y * (qq[k].x - pos.x);
+                        if (!prune || !(fabsf(cr) > corridor)) candMask |= 1u << (o0 + k);
+                    }
+                }
+                candMask &= restMask;
+                while (candMask) {
+                    const int o = __ffs(candMask) - 1;
+                    candMask &= candMask - 1;
+                    const float2 q2 = posOf[(int64_t)o * n];
+                    const v2 toPoint = mk(q2.x, q2.y) - pos;
+                    const float factor = dot(dn, toPoint) / len1;
+                    const v2 dv = toPoint - (vel * factor);
+                    const float distSq = dot(toPoint, toPoint);
+                    const float dist = factor < 0 ? distSq : dot(dv, dv);
+                    if (!(dist > dd)) {
+                        if (prune && distSq > reachSq && distSq <= passMaxSq) {
+                            ++skipped;
+                            if (prune == 2) { statMask |= 1u << o; statMarked |= 1u << o; }
+                        } else {
+                            statMask |= 1u << o;
                         }
                     }
                 }
