@@ -222,9 +222,10 @@ def run_b200(args, rank, local_rank, world):
     eng.enable_counters(True)
     eng.rerun()
     cnt = eng.counters()
+    skipped = eng.prune_counters()["skipped"]   # ball pairs the reach bound did not post (the reference solves them)
     eng.enable_counters(False)
-    cvec = torch.tensor([cnt["events"], cnt["pair_items"], cnt["quartics"], cnt["rail_items"], cnt["pocket_items"]],
-                        device="cuda", dtype=torch.float64)
+    cvec = torch.tensor([cnt["events"], cnt["pair_items"], cnt["quartics"] + skipped, cnt["rail_items"], cnt["pocket_items"],
+                         cnt["quartics"]], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(cvec)
     ev_total = float(cvec[0].item())
@@ -295,7 +296,10 @@ def run_b200(args, rank, local_rank, world):
                 "dfma_peak_gflops": 2 * peak_dfma, "ffma_peak_gflops": 2 * peak_ffma,
                 "hbm": {"achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "peak_source": hbm_src},
-                "work_per_strike": {"events": per_rank[0] / mine, "quartics": per_rank[2] / mine}}
+                "work_per_strike": {"events": per_rank[0] / mine, "quartics": per_rank[2] / mine,
+                                    "quartics_solved": per_rank[5] / mine},
+                "work_note": "algorithmic work = what the reference computes for these strikes (SURVEY.md 8d); the reach "
+                             "bound (DESIGN.md 4) leaves quartics_solved of the quartics per strike to the FP64 pipe"}
 
     # ---- CPU baseline (reference's own code, bounded sample) ----------------------------------------------------
     cpu = None

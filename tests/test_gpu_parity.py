@@ -353,7 +353,8 @@ def test_pipeline_knobs_do_not_change_results(engine, table):
     vx, vy = W.grid_velocities(dirs, speeds)
     engine.set_states(pos, types, 1 << 1)
     want = engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True)
-    for env in ({"BCU_STREAMS": 1}, {"BCU_STREAMS": 3, "BCU_NO_GRAPH": 1}, {"BCU_JOBS_PER_STRIKE": 1}):
+    for env in ({"BCU_STREAMS": 1}, {"BCU_STREAMS": 3, "BCU_NO_GRAPH": 1}, {"BCU_JOBS_PER_STRIKE": 1},
+                {"BCU_PDL": 0}, {"BCU_PDL": 2, "BCU_STREAMS": 4}, {"BCU_PRUNE": 0}):
         e = _fresh_engine(table, **env)
         try:
             e.set_states(pos, types, 1 << 1)
@@ -365,6 +366,47 @@ def test_pipeline_knobs_do_not_change_results(engine, table):
                 assert np.array_equal(again[key], want[key]), (env, "pinned", key)
         finally:
             e.close()
+
+
+def test_reach_bound_and_filters_do_not_change_results(engine):
+    """The reach bound on ball pairs and the division-free rail / partner filters (bcu_items.cuh, bcu_set_prune) only
+    skip work whose result cannot be the next event.  Mode 0 makes every test and solves every quartic the reference
+    does; mode 1 (default) must give the same bits on every output, event logs included, and the audit mode (everything
+    solved, skipped jobs marked and checked against the strike's best time) must report no failure.  Random 16- and
+    22-ball tables (the moving-vs-resting noise regime of the closed form shows up about once per 5e5 such pairs, so
+    the sample is sized to contain it: ~1e8 quartics)."""
+    from billiard_ai_b200 import workloads as W
+    rng = np.random.RandomState(2024)
+    total_marked = 0
+    try:
+        engine.enable_counters(True)
+        for t in range(12):
+            n = 16 if t % 2 == 0 else 22
+            pos, types = W.random_layout(n, 7000 + t)
+            nc = 65536
+            ang = rng.uniform(0, 2 * np.pi, nc); spd = rng.uniform(50, 5000, nc)
+            vx = (spd * np.cos(ang)).astype(np.float32); vy = (spd * np.sin(ang)).astype(np.float32)
+            engine.set_states(pos, types, 1 << 1)
+            engine.set_prune(0)
+            off = {k: v.copy() for k, v in engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True).items()}
+            q_off = engine.counters()["quartics"]
+            engine.set_prune(1)
+            on = engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=True, event_log=True)
+            q_on = engine.counters()["quartics"]
+            for key in RESULT_KEYS + ("event_log",):
+                assert np.array_equal(off[key].view(np.uint32) if off[key].dtype == np.float32 else off[key],
+                                      on[key].view(np.uint32) if on[key].dtype == np.float32 else on[key]), (t, key)
+            assert q_on < q_off
+            engine.set_prune(2)
+            engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=False)
+            pc = engine.prune_counters()
+            assert pc["audit_failures"] == 0, (t, pc)
+            assert pc["skipped"] > 0   # (the exact count depends on which offers a strike's key already held when read)
+            total_marked += pc["skipped"]
+        assert total_marked > 10_000_000
+    finally:
+        engine.set_prune(1)
+        engine.enable_counters(False)
 
 
 def test_launch_larger_than_one_pipeline_pass(engine):
