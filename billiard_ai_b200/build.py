@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libbilliard_cuda.so")
-SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu"]
+SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu", "bcu_rules.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
@@ -44,12 +44,12 @@ def build(force=False, verbose=False, extra=()):
     if not force and not needs_build():
         return OUT
     os.makedirs(OBJDIR, exist_ok=True)
-    newest = max(os.path.getmtime(d) for d in _deps() if not d.endswith(".cu"))
+    newest = max(os.path.getmtime(d) for d in _deps() if not d.endswith((".cu", ".cpp")))
     flags = [f for f in NVCC_FLAGS if f not in ("-shared", "-ldl")]
     procs = []
     objs = []
     for src in SOURCES:
-        obj = os.path.join(OBJDIR, src.replace(".cu", ".o"))
+        obj = os.path.join(OBJDIR, os.path.splitext(src)[0] + ".o")
         objs.append(obj)
         spath = os.path.join(CSRC, src)
         if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(newest, os.path.getmtime(spath)):

@@ -172,6 +172,9 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
                     }
                     if (cand) railMask |= 1u << r;
                 }
+                // Pockets, first stage: discriminant of lineIntersectsCircle (:584-625).  A pocket the ball is outside of and
+                // moving away from (qb > 0, qc > 0) has two negative intersection parameters, so timeToTarget (:383-457) returns
+                // none for it whatever the rounding (q < 0, hence x0 = q / a < 0 and x1 = c / q <= -0): dropped here.
                 for (int k = 0; k < P; ++k) {
                     const PocketGeom pg = sPockets[k];
                     const v2 delta = pos - mk(pg.x, pg.y);
@@ -179,7 +182,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
                     const float qb = 2 * dot(dn, delta);
                     const float qc = dot(delta, delta) - pg.r * pg.r;
                     const float disc = qb * qb - 4 * qa * qc;
-                    if (!(disc < 0)) pocketMask |= 1u << k;
+                    if (!(disc < 0) && !(prune && qb > 0.0f && qc > 0.0f)) pocketMask |= 1u << k;
                 }
                 const float len1 = length(vel);
                 const float accLen = length(acc);

@@ -156,6 +156,30 @@ int bcu_set_id_base(bcu_engine* e, int64_t id_base);
 int bcu_comm_unique_id(const char* nccl_lib_path, void* out128);
 int bcu_comm_init(bcu_engine* e, int32_t n_ranks, int32_t rank, const void* unique_id128, const char* nccl_lib_path);
 
+/* ---- rules between breaks (host side of the multi-break search; no device work) ------------------------------
+ * The reference calls Configuration::_rules._nextSearch / _modifyState once per finished simulation that goes on to a
+ * further break (billiard_search.cpp:1407-1462); for snooker these are billiard::snooker::nextSearch
+ * (lib/billiard_snooker/src/billiard_snooker.cpp:792-822) and stateAfterBreak (:1097-1126, with replace :1053-1095 and
+ * replaceInArea :969-1046).  Ball types are integer codes, a ball is a slot of the state table (its id); `present[i]`
+ * says whether slot i is on the table, types[i] < 0 marks a slot that is not part of the frame any more. */
+typedef struct bcu_snooker_config {      /* billiard::snooker::SnookerSearchConfig, billiard_snooker.hpp:128-136 */
+    int32_t red_type;
+    int32_t color_types[6];              /* YELLOW, GREEN, BROWN, BLUE, PINK, BLACK (typesToReplace, :773-780) */
+    float spots[6][2];                   /* their spots, same order */
+    float head_rail_dir[2];
+    float diameter_squared, radius;
+    float minimum[2], maximum[2];        /* table rectangle */
+} bcu_snooker_config;
+/* nextSearch: previous_types = the types the finished break searched for, in the order of the reference's list;
+ * out_types receives up to 6 type codes (-1 = the reference's empty type name, which matches no ball). */
+int bcu_snooker_next_search(const bcu_snooker_config* cfg, int32_t n_balls, const int32_t* types, const uint8_t* present,
+                            int32_t n_previous, const int32_t* previous_types, int32_t* out_types, int32_t* out_count);
+/* stateAfterBreak: potted colours return to the table while a red is left (own spot, else the next higher free spot,
+ * else the nearest free place within 5 radii, searched in radius/2 steps).  out_ok = 0 reproduces the reference's
+ * empty State ("could not replace all balls": the candidate is dropped). */
+int bcu_snooker_state_after_break(const bcu_snooker_config* cfg, int32_t n_balls, const float* pos, const int32_t* types,
+                                  const uint8_t* present, float* out_pos, uint8_t* out_present, int32_t* out_ok);
+
 /* ---- measurement hooks -------------------------------------------------------------------------------- */
 /* CUDA-event timer on the engine's stream (the stream every kernel of this library is launched on) */
 int bcu_timer_begin(bcu_engine* e);
