@@ -1,0 +1,141 @@
+"""Multi-break search (BASELINE configs 3 and 4): billiard_ai_b200.search.search_levels on
+the GPU against a level loop written here from the oracles only -- the reference's simulate + simulationCost + validity
+(oracle port, bit-checked against the reference build), numpy selection on (cost, id), and the reference's OWN nextSearch /
+stateAfterBreak (oracle/_ref/libref_rules.so).  Solutions must agree exactly: costs, the strike of every break, end states."""
+import numpy as np
+import pytest
+
+from test_rules import RefRules
+
+pytestmark = pytest.mark.gpu
+F_VALID = 2
+
+
+@pytest.fixture(scope="module")
+def engine(table):
+    from billiard_ai_b200 import Engine
+    from billiard_ai_b200.workloads import SNOOKER_SCORES, TYPE_CODE
+    e = Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+    yield e
+    e.close()
+
+
+def _oracle_levels(port, ref_rules, pos, types, search_types, levels, beam, dirs, speeds, search_cost, repeat=False):
+    from billiard_ai_b200 import workloads as W
+    vx1, vy1 = W.grid_velocities(dirs, speeds)
+    per_state, n_speeds = len(vx1), len(speeds)
+    states = [dict(pos=np.asarray(pos, np.float32), types=np.asarray(types, np.int32), searched=list(search_types), cost=0, path=[])]
+    solutions = []
+    near_tie = False
+    for level in range(levels):
+        if not states:
+            break
+        ns = len(states)
+        spos = np.stack([s["pos"] for s in states]); stypes = np.stack([s["types"] for s in states])
+        mask = np.array([sum(1 << t for t in s["searched"] if t >= 0) for s in states], np.uint32)
+        base = np.array([s["cost"] for s in states], np.uint64)
+        cs = np.repeat(np.arange(ns, dtype=np.int32), per_state)
+        r = port.evaluate(spos, stypes, mask, cs, np.tile(vx1, ns), np.tile(vy1, ns), search_cost, base[cs], threads=8)
+        ids = np.nonzero((r["flags"] & F_VALID) != 0)[0]
+        order = ids[np.lexsort((ids, r["cost"][ids]))][:beam]
+        near_tie |= bool((r["min_gap"][order] < 1e-9).any())
+        nxt = []
+        for cid in order.tolist():
+            si, rem = divmod(cid, per_state)
+            k, j = divmod(rem, n_speeds)
+            parent = states[si]
+            path = parent["path"] + [(k, j)]
+            ft = parent["types"]
+            present = ((ft >= 0) & (((int(r["potted"][cid]) >> np.arange(len(ft))) & 1) == 0)).astype(np.uint8)
+            rest = np.where(present[:, None].astype(bool), r["final_pos"][cid], 0.0).astype(np.float32)
+            sol = dict(cost=int(r["cost"][cid]), path=path, pos=rest, present=present)
+            if level + 1 >= levels:
+                solutions.append(sol)
+                continue
+            if repeat:
+                search, ok, pos2, present2 = list(parent["searched"]), True, rest, present
+            else:
+                search = ref_rules.next_search(rest, ft, present, parent["searched"])
+                ok, pos2, present2 = ref_rules.state_after_break(rest, ft, present)
+            if not ok:
+                continue
+            on = present2.astype(bool)
+            if any(on[i] and int(ft[i]) in search for i in range(len(ft))):
+                nxt.append(dict(pos=np.where(on[:, None], pos2, 0.0).astype(np.float32), types=np.where(on, ft, -1).astype(np.int32),
+                                searched=search, cost=int(r["cost"][cid]), path=path))
+            else:
+                sol["pos"], sol["present"] = pos2, present2
+                solutions.append(sol)
+        states = nxt
+    solutions.sort(key=lambda s: s["cost"])
+    return solutions, near_tie
+
+
+def _compare(got, want):
+    assert len(got) == len(want) and len(got) > 0
+    for g, w in zip(got, want):
+        assert g["cost"] == w["cost"]
+        assert list(zip(g["dirs"], g["speeds"])) == w["path"]
+        assert np.array_equal(g["present"], w["present"])
+        on = g["present"].astype(bool)
+        assert np.array_equal(g["pos"][on].view(np.uint32), w["pos"][on].view(np.uint32))
+
+
+@pytest.mark.parametrize("seed", [22, 5])
+def test_snooker_three_break_search_matches_the_oracle_loop(engine, port, seed):
+    """Config-4 shape at oracle size: 22-ball snooker frame, RED first, 3 breaks, beam 24, 48 x 6 strikes per state;
+    colours potted after a red are re-spotted by the rules before the next break."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import SnookerRules
+    from billiard_ai_b200.search import search_levels
+    rules = SnookerRules()
+    ref_rules = RefRules(rules)
+    pos, types = W.snooker22_open(seed)
+    dirs, speeds = W.grid(48, 6)
+    stats = []
+    got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 24, dirs, speeds, rules, stats=stats)
+    want, near_tie = _oracle_levels(port, ref_rules, pos, types, [W.TYPE_CODE["RED"]], 3, 24, dirs, speeds, W.GRID_SEARCH_COST)
+    if near_tie:
+        pytest.skip("a selected strike has two events within 1e-9 s (north_star tie clause)")
+    _compare(got, want)
+    assert max(s["breaks"] for s in got) == 3 and len(stats) == 3
+    assert any(len(set(np.nonzero(s["present"])[0])) < 22 for s in got)
+
+
+def test_pool_three_break_beam_search_matches_the_oracle_loop(engine, port):
+    """Config-3 shape at oracle size: 16-ball pool frame (seed 16), 3 breaks, beam 32, 64 x 4 strikes per state, the
+    'repeat' rule set (the reference ships no pool rules; rules.py)."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import RepeatRules
+    from billiard_ai_b200.search import search_levels
+    pos, types = W.random_layout(16, 16)
+    dirs, speeds = W.grid(64, 4)
+    got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 32, dirs, speeds, RepeatRules())
+    want, near_tie = _oracle_levels(port, None, pos, types, [W.TYPE_CODE["RED"]], 3, 32, dirs, speeds, W.GRID_SEARCH_COST,
+                                    repeat=True)
+    if near_tie:
+        pytest.skip("a selected strike has two events within 1e-9 s (north_star tie clause)")
+    _compare(got, want)
+    assert got[0]["breaks"] == 3
+
+
+def test_config3_full_size_properties(engine):
+    """BASELINE config 3 at full size: 16 balls, 3 breaks, beam 1024, 256 x 16 strikes per beam state (millions of
+    strikes in levels 2 and 3).  Size-independent properties: costs ascend, every solution pots at least one ball per break (cost
+    strictly below 3 x searchCost), accumulated costs never decrease along a path, and a second run returns the same list."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import RepeatRules
+    from billiard_ai_b200.search import search_levels
+    pos, types = W.random_layout(16, 16)
+    dirs, speeds = W.grid(256, 16)
+    stats = []
+    a = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 1024, dirs, speeds, RepeatRules(), stats=stats)
+    b = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 1024, dirs, speeds, RepeatRules())
+    assert len(a) == len(b) == 1024
+    assert [s["cost"] for s in a] == [s["cost"] for s in b] and [s["dirs"] for s in a] == [s["dirs"] for s in b]
+    costs = np.array([s["cost"] for s in a])
+    assert (np.diff(costs) >= 0).all() and costs.max() < 3 * W.GRID_SEARCH_COST
+    assert all(st["candidates"] == st["states"] * 4096 for st in stats) and stats[1]["states"] == stats[0]["beam"]
+    assert stats[2]["candidates"] >= 1_000_000
+    print(stats)
+    assert all(int(s["present"].sum()) <= 16 - 3 for s in a)   # one ball at least potted per break
