@@ -222,9 +222,14 @@ def run_b200(args, rank, local_rank, world):
     eng.enable_counters(True)
     eng.rerun()
     cnt = eng.counters()
-    skipped = eng.prune_counters()["skipped"]   # ball pairs the reach bound did not post (the reference solves them)
+    eng.set_prune(2)            # audit launch: every quartic the reference solves is solved and counted
+    eng.rerun()
+    cnt_ref = eng.counters()
+    audit = eng.prune_counters()
+    assert audit["audit_failures"] == 0, audit
+    eng.set_prune(1)
     eng.enable_counters(False)
-    cvec = torch.tensor([cnt["events"], cnt["pair_items"], cnt["quartics"] + skipped, cnt["rail_items"], cnt["pocket_items"],
+    cvec = torch.tensor([cnt["events"], cnt["pair_items"], cnt_ref["quartics"], cnt["rail_items"], cnt["pocket_items"],
                          cnt["quartics"]], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(cvec)
