@@ -92,30 +92,46 @@ constexpr float PRUNE_MIN_LEADING = 4e-3f;   // m^2/s^4; moving-vs-resting pairs
 constexpr float PRUNE_MIN_SIN_SQ = 1e-2f;
 constexpr uint32_t JOB_MARK = 0x80000000u;   // audit: the bound would have skipped this job
 
-__global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
-    const LaunchParams& p = *pp;
-    extern __shared__ uint16_t smemQ[];
-    __shared__ ItemCounts cnt;
-    __shared__ uint32_t sEnt[ITEM_BLOCK];
-    __shared__ float sT[ITEM_BLOCK];
-    __shared__ uint32_t sJobBase;
-    __shared__ RailGeom sRails[MAX_RAILS];
-    __shared__ float sDetQV[MAX_RAILS];
-    __shared__ float sRailLenSq[MAX_RAILS];   // |end - start|^2, or -1 when the component u is divided by is too short to filter on
-    __shared__ PocketGeom sPockets[MAX_POCKETS];
-    const unsigned FULL = 0xffffffffu;
-    const int tid = threadIdx.x, lane = tid & 31;
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    const int R = p.table->nRails, P = p.table->nPockets, NB = p.states.nBalls;
+// shared memory of the items stage (one instance per CTA)
+struct ItemShared {
+    ItemCounts cnt;
+    uint32_t jobBase;
+    uint32_t ent[ITEM_BLOCK];
+    float T[ITEM_BLOCK];
+    RailGeom rails[MAX_RAILS];
+    float detQV[MAX_RAILS];
+    float railLenSq[MAX_RAILS];   // |end - start|^2, or -1 when the component u is divided by is too short to filter on
+    PocketGeom pockets[MAX_POCKETS];
+};
+
+// table geometry -> shared memory; depends on nothing a kernel of the launch writes
+__device__ __forceinline__ void items_prologue(ItemShared& sh, const LaunchParams& p) {
+    const int tid = threadIdx.x;
+    const int R = p.table->nRails, P = p.table->nPockets;
     for (int i = tid; i < R; i += ITEM_BLOCK) {
         const RailGeom rg = p.table->rails[i];
-        sRails[i] = rg;
-        sDetQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
+        sh.rails[i] = rg;
+        sh.detQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
         const float used = fabsf(rg.dx != 0.0f ? rg.dx : rg.dy);
-        sRailLenSq[i] = used >= 5.0f ? rg.dx * rg.dx + rg.dy * rg.dy : -1.0f;
+        sh.railLenSq[i] = used >= 5.0f ? rg.dx * rg.dx + rg.dy * rg.dy : -1.0f;
     }
-    for (int i = tid; i < P; i += ITEM_BLOCK) sPockets[i] = p.table->pockets[i];
-    cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
+    for (int i = tid; i < P; i += ITEM_BLOCK) sh.pockets[i] = p.table->pockets[i];
+}
+
+// `bid` of `nb` CTAs work on this round (items_kernel passes its grid)
+__device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, const LaunchParams& p, const PipeWorkspace& w, int round,
+                                           unsigned bid, unsigned nb) {
+    ItemCounts& cnt = sh.cnt;
+    uint32_t* sEnt = sh.ent;
+    float* sT = sh.T;
+    uint32_t& sJobBase = sh.jobBase;
+    const RailGeom* sRails = sh.rails;
+    const float* sDetQV = sh.detQV;
+    const float* sRailLenSq = sh.railLenSq;
+    const PocketGeom* sPockets = sh.pockets;
+    const unsigned FULL = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int R = p.table->nRails, P = p.table->nPockets, NB = p.states.nBalls;
     const uint32_t nDyn = w.counts[4 * round + 1];
     if (nDyn == 0) return;
     uint16_t* qPairs = smemQ;
@@ -129,7 +145,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
     const int prune = w.pruneMode;
     unsigned long long skipped = 0;   // counters / audit only
 
-    for (uint32_t base = blockIdx.x * ITEM_BLOCK; base < nDyn; base += gridDim.x * ITEM_BLOCK) {
+    for (uint32_t base = bid * ITEM_BLOCK; base < nDyn; base += nb * ITEM_BLOCK) {
         if (tid == 0) { cnt.pairs = 0; cnt.dynPairs = 0; }
         __syncthreads();
 
@@ -360,4 +376,14 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
         __syncthreads();
     }
     if (p.out.counters && skipped) atomicAdd(&p.out.counters[5], skipped);
+}
+
+__global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    extern __shared__ uint16_t smemQ[];
+    __shared__ ItemShared sh;
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    items_prologue(sh, *pp);
+    cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
+    __syncthreads();
+    items_body(sh, smemQ, *pp, w, round, blockIdx.x, gridDim.x);
 }

@@ -144,14 +144,12 @@ __device__ __forceinline__ void mark_finished(const LaunchParams& p, int64_t s, 
 // init: toInputLayer (billiard_search.cpp:760-795) + System::append of layer 0.  One thread per strike (the per-ball
 // arrays are ball-major, [ball][strike], so consecutive threads write consecutive words).
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();   // see launch_pipeline
-    const LaunchParams& p = *pp;
-    __shared__ AppendShared ash;
+__device__ __forceinline__ void init_body(AppendShared& ash, const LaunchParams& p, const PipeWorkspace& w, unsigned bid, unsigned nb) {
     const int NB = p.states.nBalls;
     const PhysConst pc = p_phys;
     const int64_t n = w.n;
-    for (int64_t base = (int64_t)blockIdx.x * 256; base < p.nCand; base += (int64_t)gridDim.x * 256) {
+    const int BS = blockDim.x;
+    for (int64_t base = (int64_t)bid * BS; base < p.nCand; base += (int64_t)nb * BS) {
         const int64_t s = base + threadIdx.x;
         uint32_t dynMask = 0, restMask = 0;
         if (s < p.nCand) {
@@ -205,18 +203,22 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
     }
 }
 
+__global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();   // see launch_pipeline
+    __shared__ AppendShared ash;
+    init_body(ash, *pp, w, blockIdx.x, gridDim.x);
+}
+
 #include "bcu_items.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------------
 // quartic: one thread per job.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    cudaGridDependencySynchronize();
+__device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb) {
     const uint32_t posted = w.counts[4 * round + 2];
     const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
     unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
-    for (uint64_t j = (uint64_t)blockIdx.x * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)gridDim.x * QUARTIC_BLOCK) {
+    for (uint64_t j = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)nb * QUARTIC_BLOCK) {
         float co[5];
         #pragma unroll
         for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
@@ -233,6 +235,12 @@ __global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_ker
             offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
         }
     }
+}
+
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+    quartic_body(w, round, blockIdx.x, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -280,12 +288,10 @@ __device__ __forceinline__ void offer_own(unsigned long long* key, const BallRec
     if (r.nextRolling >= 0.0f) offer(key, r.nextRolling, make_code(b, CAT_ROLLING, 0));
 }
 
-__global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    const LaunchParams& p = *pp;
-    __shared__ AppendShared ash;
+__device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams& p, const PipeWorkspace& w, int round, unsigned bid,
+                                           unsigned nb) {
     const PhysConst pc = p_phys;
-    cudaGridDependencySynchronize();
+    const int BS = blockDim.x;
     const uint32_t nLive = w.counts[4 * round + 0], nDyn = w.counts[4 * round + 1];
     if (nLive == 0) return;
     const uint32_t* live = w.live + (size_t)(round & 1) * w.n;
@@ -300,10 +306,10 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
     uint32_t* liveCountNext = &w.counts[4 * (round + 1) + 0];
     uint32_t* dynCountNext = &w.counts[4 * (round + 1) + 1];
     const bool overflow = round + 1 > MAX_EVENTS;  // billiard_search.cpp:1376-1379 (every live strike has `round` events)
-    const int64_t stride = (int64_t)gridDim.x * APPLY_BLOCK;
+    const int64_t stride = (int64_t)nb * BS;
 
     // ---- the event of every live strike (createLayer :1957-1992) ----------------------------------------------------
-    for (int64_t base = (int64_t)blockIdx.x * APPLY_BLOCK; base < nLive; base += stride) {
+    for (int64_t base = (int64_t)bid * BS; base < nLive; base += stride) {
         const int64_t idx = base + threadIdx.x;
         bool appendLive = false, appendA = false, appendB = false;
         uint32_t entA = 0, entB = 0, sLive = 0;
@@ -394,7 +400,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
     }
 
     // ---- every other dynamic ball: closed-form advance to the new layer (createNodes :1907-1955) ---------------------
-    for (int64_t base = (int64_t)blockIdx.x * APPLY_BLOCK; base < nDyn; base += stride) {
+    for (int64_t base = (int64_t)bid * BS; base < nDyn; base += stride) {
         const int64_t idx = base + threadIdx.x;
         bool keep = false;
         uint32_t ent = 0;
@@ -437,18 +443,22 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
     }
 }
 
+__global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    __shared__ AppendShared ash;
+    cudaGridDependencySynchronize();
+    apply_body(ash, *pp, w, round, blockIdx.x, gridDim.x);
+}
+
 // rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
 // One warp per strike, lane = ball.
-__global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    const LaunchParams& p = *pp;
+__device__ __forceinline__ void finish_body(const LaunchParams& p, const PipeWorkspace& w, unsigned bid, unsigned nb) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int NB = p.states.nBalls;
-    cudaGridDependencySynchronize();
-    const int64_t warpsTotal = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t warpsTotal = (int64_t)nb * (blockDim.x >> 5);
     unsigned long long events = 0;
-    for (int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
+    for (int64_t s = (int64_t)bid * (blockDim.x >> 5) + (threadIdx.x >> 5); s < p.nCand; s += warpsTotal) {
         const Candidate c = decode_candidate(p, s);
         uint32_t flags = p.out.flags[s];
         int kind = K_ABSENT, type = -1;
@@ -488,6 +498,11 @@ __global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restr
         if (p.out.finalPos && lane < NB) reinterpret_cast<float2*>(p.out.finalPos)[s * NB + lane] = make_float2(q.x, q.y);
     }
     if (p.out.counters && lane == 0 && events) atomicAdd(&p.out.counters[0], events);
+}
+__global__ void __launch_bounds__(256) finish_kernel(const LaunchParams* __restrict__ pp, PipeWorkspace w) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+    finish_body(*pp, w, blockIdx.x, gridDim.x);
 }
 
 // work counters from the per-round list sizes: [1] pair items [2] quartics solved [3] rail items [4] pocket items
