@@ -290,9 +290,18 @@ def run_b200(args, rank, local_rank, world):
             hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
         hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    # DRAM traffic of one level's kernels from the committed ncu launch list (warm caches, single GPU, this workload)
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_v5_dram_per_level.json")) as f:
+            dj = json.load(f)
+        traffic = float(dj["dram_bytes_read"] + dj["dram_bytes_write"])
+        traffic_src = "profiles/r01_v5_dram_per_level.json (ncu dram__bytes_read.sum + dram__bytes_write.sum over the level's launches)"
+    except Exception:
+        pass
     ach = fp64_flop / (k_ms * 1e-3) / 1e9
     roofline = {"bound": "fp64_vector", "kernel": "strike pipeline (init + 31 x {items, quartic, apply} + finish; FP64 work = quartic_kernel)", "achieved": ach, "peak": peak_dp,
-                "unit": "GFLOP/s", "frac": ach / peak_dp, "traffic": None,
+                "unit": "GFLOP/s", "frac": ach / peak_dp, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "measured in this run: un-fused DADD+DMUL issue rate (FMA contraction is forbidden on "
                                "this path); DFMA rate x2 listed for context",
                 "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (t_ms / args.steps),
