@@ -63,11 +63,15 @@ __device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint16_t
 // the relative motion runs along a line (every moving-vs-resting pair: dA || dV) the depressed quartic is biquadratic up to
 // quantisation noise, Ferrari's S is then ~0 unless all four roots are real, and q/S is rounding noise that the reference
 // turns into an "event" about once in 5e5 such pairs.  Those results are reproduced bit for bit by solving the quartic;
-// the bound is only applied where the solver is well conditioned:
+// the bound is only applied where the solver resolves the roots:
 //   * moving vs resting: only if the ball's polynomial passes the partner completely before its turning point
-//     (|dP| + d + 5 mm <= 0.99 v^2 / 2|a|: four real roots, S = half the sum of the two larger ones),
-//   * moving vs moving: only if the leading coefficient is >= 4e-3 (not nearly cubic) and the angle between dA and dV is
-//     >= 5.7 degrees (sin^2 >= 1e-2: not nearly collinear).
+//     (|dP| + d + 5 mm <= 0.99 v^2 / 2|a|: four real roots, S = half the sum of the two larger ones); every other resting
+//     partner is solved (a partner beyond the turning point has four complex roots and "should" give no event, but that is
+//     exactly where the closed form is noise: DESIGN.md section 4);
+//   * moving vs moving: only if dA and dV are more than 0.57 degrees apart (sin^2 >= 1e-4: q is then 4 orders of magnitude
+//     above the quantisation noise that makes the collinear case fragile) and the leading coefficient is >= 1e-5 (a = 0
+//     exactly makes the reference return "none" before solving; in between the quartic is nearly cubic).  Audits with
+//     both guards removed found no failure either (5.4e8 marked jobs); they are kept as margin.
 // On top of the bound 2 ms and 2 mm of slack are left for the rounding of the solver in these regimes.  The strike's key
 // only decreases during a round, so any value read from it is a valid T.  mode 2 (audit) posts everything and marks the
 // jobs the bound would have skipped; quartic_kernel then counts the marked jobs whose result would have mattered
@@ -88,8 +92,14 @@ __device__ __forceinline__ float reach_ball(const Reach& r, float v, float a) {
     const float lin = v * r.t, quad = 0.5f * a * r.t * r.t;
     return (lin > quad ? lin : quad) + 1e-3f * (v + a * r.t);
 }
-constexpr float PRUNE_MIN_LEADING = 4e-3f;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
-constexpr float PRUNE_MIN_SIN_SQ = 1e-2f;
+#ifndef PRUNE_MIN_LEADING_V
+#define PRUNE_MIN_LEADING_V 1e-5f
+#endif
+#ifndef PRUNE_MIN_SIN_SQ_V
+#define PRUNE_MIN_SIN_SQ_V 1e-4f
+#endif
+constexpr float PRUNE_MIN_LEADING = PRUNE_MIN_LEADING_V;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
+constexpr float PRUNE_MIN_SIN_SQ = PRUNE_MIN_SIN_SQ_V;
 constexpr uint32_t JOB_MARK = 0x80000000u;   // audit: the bound would have skipped this job
 
 // shared memory of the items stage (one instance per CTA)
@@ -159,46 +169,60 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
             const int b = (int)(ent & 31u);
             const int64_t g = (int64_t)b * n + s;
             const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g], q3 = w.acc[g];
-            const int lastRail = meta_last_rail(w.meta[g]);
+            const uint32_t metaWord = w.meta[g];
+            const int lastRail = meta_last_rail(metaWord);
             const uint32_t restMask = w.restMask[s], dynMask = w.dynMask[s];
             unsigned long long keyNow = __ldcg(key + s);   // rest / rolling offers of the strike (and whatever else is in)
             const v2 pos = mk(q0.x, q0.y), vel = mk(q1.x, q1.y), dn = mk(q2n.x, q2n.y), acc = mk(q3.x, q3.y);
             dynPairMask = dynMask & ~((2u << b) - 1u);   // dynamic partners o > b (one job covers both orders)
             if (!is_zero(vel)) {
                 uint32_t railMask = 0, pocketMask = 0;
-                // Rails, pass A (no division): which rails can the half-line cross at all?  The exact test below divides twice
-                // per rail; here a rail is dropped only when the exact test is certain to fail: the intersection parameter
-                // t = N / detDV is negative by more than any rounding (N detDV < 0, |t| > 1e-10), or -- for lines at more than
-                // ~1.1 degrees (sin^2 >= 4e-4), where both this estimate and the reference's u are accurate to < 1e-2 -- the
-                // crossing lies more than 5 % of the segment outside it.  Everything else is a candidate (prune mode 0: all).
-                const float speedSq = dot(vel, vel);
-                for (int r = 0; r < R; ++r) {
-                    const RailGeom rg = sRails[r];
-                    const float detDV = vel.x * rg.dy - vel.y * rg.dx;
-                    const float nT = (rg.dx * pos.y - rg.dy * pos.x) + sDetQV[r];
-                    bool cand = r != lastRail && detDV != 0.0f;
-                    if (prune) {
-                        const bool behind = nT * detDV < 0.0f && fabsf(nT) > 1e-10f * fabsf(detDV);
-                        const float lenSq = sRailLenSq[r];
-                        const float nU = (pos.x - rg.sx) * vel.y - (pos.y - rg.sy) * vel.x;   // u = nU / -detDV
-                        const float den = -detDV, sgnU = den < 0.0f ? -nU : nU, aden = fabsf(den);
-                        const bool wellCond = lenSq > 0.0f && detDV * detDV >= 4e-4f * (speedSq * lenSq);
-                        const bool outside = wellCond && (sgnU < -0.05f * aden || sgnU > 1.05f * aden);
-                        cand = cand && !behind && !outside;
+                // The rail and pocket candidates are functions of the ball's LINE of motion (plus "already behind", which only
+                // grows): a ball that was merely advanced since the last round (kind MOVING: same direction, further along)
+                // reuses the masks stored when its direction was set; the exact stages below sort out what it has passed since.
+                const bool reuse = prune && meta_kind(metaWord) == K_MOVING && R <= 24;
+                if (reuse) {
+                    const uint32_t c2 = w.lineCand[g];
+                    railMask = c2 & 0xffffffu;
+                    pocketMask = c2 >> 24;
+                } else {
+                    // Rails, pass A (no division): which rails can the half-line cross at all?  The exact test below divides twice
+                    // per rail; here a rail is dropped only when the exact test is certain to fail: the intersection parameter
+                    // t = N / detDV is negative by more than any rounding (N detDV < 0, |t| > 1e-10), or -- for lines at more than
+                    // ~1.1 degrees (sin^2 >= 4e-4), where both this estimate and the reference's u are accurate to < 1e-2 -- the
+                    // crossing lies more than 5 % of the segment outside it.  Everything else is a candidate (prune mode 0: all).
+                    const float speedSq = dot(vel, vel);
+                    for (int r = 0; r < R; ++r) {
+                        const RailGeom rg = sRails[r];
+                        const float detDV = vel.x * rg.dy - vel.y * rg.dx;
+                        const float nT = (rg.dx * pos.y - rg.dy * pos.x) + sDetQV[r];
+                        bool cand = r != lastRail && detDV != 0.0f;
+                        if (prune) {
+                            const bool behind = nT * detDV < 0.0f && fabsf(nT) > 1e-10f * fabsf(detDV);
+                            const float lenSq = sRailLenSq[r];
+                            const float nU = (pos.x - rg.sx) * vel.y - (pos.y - rg.sy) * vel.x;   // u = nU / -detDV
+                            const float den = -detDV, sgnU = den < 0.0f ? -nU : nU, aden = fabsf(den);
+                            const bool wellCond = lenSq > 0.0f && detDV * detDV >= 4e-4f * (speedSq * lenSq);
+                            const bool outside = wellCond && (sgnU < -0.05f * aden || sgnU > 1.05f * aden);
+                            cand = cand && !behind && !outside;
+                        }
+                        if (cand) railMask |= 1u << r;
                     }
-                    if (cand) railMask |= 1u << r;
-                }
-                // Pockets, first stage: discriminant of lineIntersectsCircle (:584-625).  A pocket the ball is outside of and
-                // moving away from (qb > 0, qc > 0) has two negative intersection parameters, so timeToTarget (:383-457) returns
-                // none for it whatever the rounding (q < 0, hence x0 = q / a < 0 and x1 = c / q <= -0): dropped here.
-                for (int k = 0; k < P; ++k) {
-                    const PocketGeom pg = sPockets[k];
-                    const v2 delta = pos - mk(pg.x, pg.y);
-                    const float qa = 1;
-                    const float qb = 2 * dot(dn, delta);
-                    const float qc = dot(delta, delta) - pg.r * pg.r;
-                    const float disc = qb * qb - 4 * qa * qc;
-                    if (!(disc < 0) && !(prune && qb > 0.0f && qc > 0.0f)) pocketMask |= 1u << k;
+                    // Pockets, first stage: discriminant of lineIntersectsCircle (:584-625).  A pocket the ball is outside of and
+                    // moving away from (qb > 0, qc > 0) has two negative intersection parameters, so timeToTarget (:383-457) returns
+                    // none for it whatever the rounding (q < 0, hence x0 = q / a < 0 and x1 = c / q <= -0): dropped here.
+                    for (int k = 0; k < P; ++k) {
+                        const PocketGeom pg = sPockets[k];
+                        const v2 delta = pos - mk(pg.x, pg.y);
+                        const float qa = 1;
+                        const float qb = 2 * dot(dn, delta);
+                        const float qc = dot(delta, delta) - pg.r * pg.r;
+                        const float disc = qb * qb - 4 * qa * qc;
+                        // (with the filters on, a pocket is kept down to 0.4 mm outside the tangent: the mask outlives this position)
+                        const float slack = prune ? 1e-5f * (qb * qb + 4.0f * (dot(delta, delta) + pg.r * pg.r)) + 1.0f : 0.0f;
+                        if (!(disc < -slack) && !(prune && qb > 0.0f && qc > 0.0f)) pocketMask |= 1u << k;
+                    }
+                    if (prune && R <= 24) w.lineCand[g] = railMask | (pocketMask << 24);
                 }
                 const float len1 = length(vel);
                 const float accLen = length(acc);
@@ -227,6 +251,11 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                 while (pocketMask) {
                     const int k = __ffs(pocketMask) - 1;
                     pocketMask &= pocketMask - 1;
+                    if (reuse) {   // passed since the mask was made? (outside and moving away: none, see the first stage)
+                        const PocketGeom pg = sPockets[k];
+                        const v2 delta = pos - mk(pg.x, pg.y);
+                        if (2 * dot(dn, delta) > 0.0f && dot(delta, delta) - pg.r * pg.r > 0.0f) continue;
+                    }
                     float t;
                     if (time_to_pocket(sPockets[k], pos, dn, vel, acc, &t) && t == t) {
                         const unsigned long long k2 = ((unsigned long long)ordered_bits(t) << 32) | make_code(b, CAT_POCKET, k);
@@ -273,7 +302,11 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                     const float distSq = dot(toPoint, toPoint);
                     const float dist = factor < 0 ? distSq : dot(dv, dv);
                     if (!(dist > dd)) {
-                        if (prune && distSq > reachSq && distSq <= passMaxSq) {
+                        bool skip = false;
+                        if (prune) {
+                            if (distSq <= passMaxSq) skip = distSq > reachSq;   // passed completely before the turning point
+                        }
+                        if (skip) {
                             ++skipped;
                             if (prune == 2) { statMask |= 1u << o; statMarked |= 1u << o; }
                         } else {

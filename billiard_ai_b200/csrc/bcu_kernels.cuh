@@ -70,6 +70,7 @@ struct PipeWorkspace {
     float2* acc;
     float* nextRolling;        // < 0: none  (System::_nextRolling, type.cpp:478-527)
     uint32_t* meta;            // kind | rolling << 8 | (lastRail + 1) << 16 | (type + 1) << 24
+    uint32_t* lineCand;        // rail (bits 0-23) and pocket (24-31) candidates of the ball's current line of motion (bcu_items.cuh)
     // per strike
     unsigned long long* key;   // [3][n] (ordered time bits << 32 | evaluation-order code), by round % 3
     float* T;                  // [2][n] layer time, by round & 1

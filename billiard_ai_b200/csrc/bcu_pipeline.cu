@@ -544,6 +544,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     const size_t oPos = take(nb * sizeof(float2)), oVel = take(nb * sizeof(float2)), oVn = take(nb * sizeof(float2));
     const size_t oAcc = take(nb * sizeof(float2)), oNr = take(nb * sizeof(float));
     const size_t oMeta = take(nb * sizeof(uint32_t));
+    const size_t oLc = take(nb * sizeof(uint32_t));
     const size_t oKey = take((size_t)3 * n * sizeof(unsigned long long));
     const size_t oT = take((size_t)2 * n * sizeof(float));
     const size_t oDm = take((size_t)n * sizeof(uint32_t)), oRm = take((size_t)n * sizeof(uint32_t));
@@ -556,7 +557,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
         w.base = layout->base;
         w.pos = reinterpret_cast<float2*>(b + oPos); w.vel = reinterpret_cast<float2*>(b + oVel);
         w.vn = reinterpret_cast<float2*>(b + oVn); w.acc = reinterpret_cast<float2*>(b + oAcc);
-        w.nextRolling = reinterpret_cast<float*>(b + oNr); w.meta = reinterpret_cast<uint32_t*>(b + oMeta);
+        w.nextRolling = reinterpret_cast<float*>(b + oNr); w.meta = reinterpret_cast<uint32_t*>(b + oMeta); w.lineCand = reinterpret_cast<uint32_t*>(b + oLc);
         w.key = reinterpret_cast<unsigned long long*>(b + oKey); w.T = reinterpret_cast<float*>(b + oT);
         w.dynMask = reinterpret_cast<uint32_t*>(b + oDm); w.restMask = reinterpret_cast<uint32_t*>(b + oRm);
         w.live = reinterpret_cast<uint32_t*>(b + oLive); w.dyn = reinterpret_cast<uint32_t*>(b + oDyn);

@@ -13,7 +13,7 @@ struct Stats {
     double maxRho = -1e30;            // max over hits of rho(t_hit): must stay <= 0
     uint64_t winnerIsPair = 0;
 };
-struct Job { int i, j; float L, vrel, a, vi, vj, ai, aj, sin2; bool has; float t; bool isStatic; };
+struct Job { int i, j; float L, vrel, a, vi, vj, ai, aj, sin2; bool has; float t; bool isStatic; double guard; int beyond; };
 
 static inline float rho(const Job& jb, float T, float d) {
     T = T + 2e-3f;
@@ -76,6 +76,26 @@ static Event nextEventStudy(const Sim& s, Stats& st) {
             V dA = (bi.acc - bj.acc) * (1.0f / 1000.0f);
             jb.a = 0.25f * dot(dA, dA);
             { V dV = (bi.vel - bj.vel) * (1.0f / 1000.0f); float cr = dA.x * dV.y - dA.y * dV.x; jb.sin2 = cr * cr / (dot(dA, dA) * dot(dV, dV)); }
+            jb.guard = -1; jb.beyond = 0;
+            if (isStatic) {   // the kernel's beyond_turning_point() quantities
+                V tp = bj.pos - bi.pos; V dn = bi.vn;
+                float along = dot(dn, tp);
+                float factor = along / len(bi.vel);
+                V dv = tp - bi.vel * factor;
+                float perpSq = dot(dv, dv), dd = g.diameter * g.diameter;
+                float hSq = dd - perpSq;
+                float stop = (jb.vi * jb.vi) / (2.0f * jb.ai);
+                if (factor >= 0 && hSq >= 25.0f && along - std::sqrt(hSq) > 1.05f * stop + 5.0f) {
+                    jb.beyond = 1;
+                    float toMeter = 1.0f / 1000.0f, dm = g.diameter * toMeter;
+                    V dA = (bi.acc - bj.acc) * toMeter, dV = (bi.vel - bj.vel) * toMeter, dP = (bi.pos - bj.pos) * toMeter;
+                    double a = floorf(0.25f * dot(dA, dA) * 1000000) / 1000000, b = floorf(dot(dA, dV) * 1000000) / 1000000;
+                    double c = floorf((dot(dA, dP) + dot(dV, dV)) * 1000000) / 1000000, d = floorf(2 * (dot(dV, dP)) * 1000000) / 1000000;
+                    double pp = (8 * a * c - 3 * b * b) / (8 * a * a), qq = (b * b * b - 4 * a * b * c + 8 * a * a * d) / (8 * a * a * a);
+                    double S = std::fabs(qq) * jb.ai / (8.0 * std::sqrt(hSq));
+                    jb.guard = (pp > 0) ? S * S / (1e-12 * (1.0 + pp)) : -2;
+                }
+            }
             jobs.push_back(jb);
         }
     }
@@ -83,6 +103,14 @@ static Event nextEventStudy(const Sim& s, Stats& st) {
     st.steps++;
     st.jobs += jobs.size();
     if (best.type == EV_COLLISION) st.winnerIsPair++;
+    for (auto& jb : jobs) {
+        if (jb.beyond && getenv("STUDY_BEYOND")) {
+            static uint64_t nB = 0, nHit = 0, nGuardOk = 0; static double minHitFree = 1e300;
+            nB++; if (jb.guard >= 1.0) nGuardOk++;
+            if (jb.has) { nHit++; fprintf(stderr, "BEYOND-HIT guard %.3g t %.6g vi %g ai %g L %g a %g\n", jb.guard, jb.t, jb.vi, jb.ai, jb.L, jb.a); }
+            if (nB % 200000 == 0) fprintf(stderr, "beyond %llu guard-ok %llu hits %llu\n", (unsigned long long)nB, (unsigned long long)nGuardOk, (unsigned long long)nHit);
+        }
+    }
     // single pass
     for (auto& jb : jobs) {
         (jb.isStatic ? st.jobsStatic : st.jobsDyn)++;
