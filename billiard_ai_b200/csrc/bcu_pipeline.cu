@@ -106,8 +106,8 @@ __device__ __forceinline__ Candidate decode_candidate(const LaunchParams& p, int
 // Reserves list slots for up to three predicates per thread with ONE global atomicAdd per predicate and CTA (same-address
 // atomics are the serial part of stream compaction).  All threads of the CTA must call; *slotK is valid where predK.
 struct AppendShared {
-    uint32_t warpCount[3][8];
-    uint32_t warpBase[3][8];
+    uint32_t warpCount[4][8];
+    uint32_t warpBase[4][8];
 };
 template <int NPRED>
 __device__ __forceinline__ void cta_reserve(AppendShared& sh, const bool (&pred)[NPRED], uint32_t* const (&counter)[NPRED],
@@ -309,7 +309,10 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
     const int64_t stride = (int64_t)nb * BS;
 
     // ---- the event of every live strike (createLayer :1957-1992) ----------------------------------------------------
-    for (int64_t base = (int64_t)bid * BS; base < nLive; base += stride) {
+    // One pass over both lists: tile i of the live strikes and tile i of the dynamic balls are handled by the same CTA
+    // iteration (they touch different balls), so their memory round trips overlap and one list reservation serves both.
+    const int64_t nMax = nLive > nDyn ? (int64_t)nLive : (int64_t)nDyn;
+    for (int64_t base = (int64_t)bid * BS; base < nMax; base += stride) {
         const int64_t idx = base + threadIdx.x;
         bool appendLive = false, appendA = false, appendB = false;
         uint32_t entA = 0, entB = 0, sLive = 0;
@@ -388,20 +391,7 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
                 else appendLive = true;
             }
         }
-        {
-            const bool pred[3] = {appendLive, appendA, appendB};
-            uint32_t* const counter[3] = {liveCountNext, dynCountNext, dynCountNext};
-            uint32_t slot[3];
-            cta_reserve<3>(ash, pred, counter, slot);
-            if (appendLive) liveNext[slot[0]] = sLive;
-            if (appendA) dynNext[slot[1]] = entA;
-            if (appendB) dynNext[slot[2]] = entB;
-        }
-    }
-
-    // ---- every other dynamic ball: closed-form advance to the new layer (createNodes :1907-1955) ---------------------
-    for (int64_t base = (int64_t)bid * BS; base < nDyn; base += stride) {
-        const int64_t idx = base + threadIdx.x;
+        // ---- every other dynamic ball: closed-form advance to the new layer (createNodes :1907-1955) -----------------
         bool keep = false;
         uint32_t ent = 0;
         if (idx < nDyn && !overflow) {
@@ -434,11 +424,14 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
             }
         }
         {
-            const bool pred[1] = {keep};
-            uint32_t* const counter[1] = {dynCountNext};
-            uint32_t slot[1];
-            cta_reserve<1>(ash, pred, counter, slot);
-            if (keep) dynNext[slot[0]] = ent;
+            const bool pred[4] = {appendLive, appendA, appendB, keep};
+            uint32_t* const counter[4] = {liveCountNext, dynCountNext, dynCountNext, dynCountNext};
+            uint32_t slot[4];
+            cta_reserve<4>(ash, pred, counter, slot);
+            if (appendLive) liveNext[slot[0]] = sLive;
+            if (appendA) dynNext[slot[1]] = entA;
+            if (appendB) dynNext[slot[2]] = entB;
+            if (keep) dynNext[slot[3]] = ent;
         }
     }
 }
