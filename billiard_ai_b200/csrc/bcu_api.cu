@@ -82,6 +82,9 @@ struct bcu_engine {
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
     int pruneMode = 1;                  // reach bound on ball pairs (bcu_set_prune): 0 off, 1 on, 2 audit
     uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
+    void* hBeam = nullptr;           // pinned staging for bcu_fetch_beam
+    size_t hBeamCap = 0;
+    const void* beamBlock = nullptr; // the record block bcu_fetch_beam reads (local block on one rank, else the merged one)
     int pipeStreams = 2;             // BCU_STREAMS: parts of a launch in flight at once (measured: 2 best at 65 536 strikes)
     cudaStream_t pipeStream[PIPE_MAX_STREAMS] = {};
     cudaEvent_t pipeDone[PIPE_MAX_STREAMS] = {};
@@ -277,6 +280,7 @@ void bcu_destroy(bcu_engine* e) {
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
     if (e->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->ncclComm);
     if (e->hOverflow) cudaFreeHost(e->hOverflow);
+    if (e->hBeam) cudaFreeHost(e->hBeam);
     for (int g = 0; g < PIPE_MAX_STREAMS; ++g) {
         if (e->pipeDone[g]) cudaEventDestroy(e->pipeDone[g]);
         if (e->pipeStream[g]) cudaStreamDestroy(e->pipeStream[g]);
@@ -358,7 +362,11 @@ static void fill_common(bcu_engine* e, LaunchParams& p, int64_t n, bool wantPos,
     p.out.counters = e->countersOn ? e->dCounters.p : nullptr;
 }
 
-static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
+static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out);
+
+// `out` (batch path, single wave): the device->host copies of the results are queued right behind the launch, before the
+// host waits for it, so the transfer starts the moment the last kernel ends (a retry after a job-queue overflow copies again)
+static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_results* out = nullptr, bool* copied = nullptr) {
     if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
     if (p.out.eventLog && trace) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
     CK(cudaEventRecord(e->evStart, e->stream));
@@ -446,6 +454,12 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
                 }
                 if (useGraph) CK(cudaGraphLaunch(e->pipeGraph, e->stream));
                 e->launches += (int64_t)G * pipeline_launch_count();
+                CK(cudaEventRecord(e->evStop, e->stream));
+                if (out && nParts <= G) {
+                    int rc = enqueue_copy_back(e, 0, p.nCand, out);
+                    if (rc) return rc;
+                    if (copied) *copied = true;
+                }
                 CK(cudaStreamSynchronize(e->stream));
                 bool overflow = false;
                 for (int g = 0; g < G; ++g) overflow |= e->hOverflow[g] != 0;
@@ -455,11 +469,11 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace) {
             }
         }
     }
-    CK(cudaEventRecord(e->evStop, e->stream));
+    if (trace) CK(cudaEventRecord(e->evStop, e->stream));
     return BCU_OK;
 }
 
-static int copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
+static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
     if (!out) return BCU_OK;
     if (out->cost) CK(cudaMemcpyAsync(out->cost, e->dCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
     if (out->flags) CK(cudaMemcpyAsync(out->flags, e->dFlags.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
@@ -475,6 +489,12 @@ static int copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results
         CK(cudaMemcpyAsync(out->event_log, e->dEventLog.p + (size_t)offset * 32, (size_t)n * 32 * sizeof(int4),
                            cudaMemcpyDeviceToHost, e->stream));
     }
+    return BCU_OK;
+}
+
+static int copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
+    int rc = enqueue_copy_back(e, offset, n, out);
+    if (rc) return rc;
     CK(cudaStreamSynchronize(e->stream));
     return BCU_OK;
 }
@@ -486,8 +506,6 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     if (n < 0 || (n > 0 && (!stateIdx || !vx || !vy || !searchCost || !baseCost)))
         return fail(e, BCU_ERR_INVALID, "bcu_evaluate: bad arguments");
     if (n == 0) return BCU_OK;
-    for (int64_t i = 0; i < n; ++i)
-        if (stateIdx[i] < 0 || stateIdx[i] >= e->nStates) return fail(e, BCU_ERR_INVALID, "bcu_evaluate: state index out of range");
     CK(cudaSetDevice(e->device));
     CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n));
     CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
@@ -500,15 +518,24 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     CK(cudaMemcpyAsync(e->dVy.p, vy, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dSearchCost.p, searchCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dBaseCost.p, baseCost, n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    // argument check while the copies are in flight (nothing has been launched on them yet)
+    int32_t lowest = 0, highest = 0;
+    for (int64_t i = 0; i < n; ++i) { const int32_t s = stateIdx[i]; lowest = s < lowest ? s : lowest; highest = s > highest ? s : highest; }
+    if (lowest < 0 || highest >= e->nStates) {
+        cudaStreamSynchronize(e->stream);
+        return fail(e, BCU_ERR_INVALID, "bcu_evaluate: state index out of range");
+    }
     LaunchParams p;
     fill_common(e, p, n, true, wantLog);
     (void)wantPos;
     p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
     p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
-    rc = run(e, p, false);
-    if (rc) return rc;
-    e->last = p; e->haveLast = true; e->lastFirst = e->idBase;
-    return copy_back(e, 0, n, out);
+    e->last = p;   // (the copies check what the launch produces)
+    bool copied = false;
+    rc = run(e, p, false, out, &copied);
+    if (rc) { e->haveLast = false; return rc; }
+    e->haveLast = true; e->lastFirst = e->idBase;
+    return copied ? BCU_OK : copy_back(e, 0, n, out);
 }
 
 int bcu_evaluate_grid(bcu_engine* e, int32_t nDirs, int32_t nSpeeds, const float* dirs, const float* speeds,
@@ -566,7 +593,7 @@ int bcu_topk(bcu_engine* e, int32_t k, uint64_t* outCost, uint64_t* outId, int32
     CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
     CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
                    e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
-    e->launches += 3;
+    e->launches += 4;
     int32_t valid = 0;
     CK(cudaMemcpyAsync(outCost, e->dTopCost.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
     CK(cudaMemcpyAsync(outId, e->dTopId.p, k * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
@@ -636,7 +663,7 @@ static int topk_device(bcu_engine* e, int32_t k) {
     CK(e->dTopkScratch.reserve(sb)); CK(e->dTopCost.reserve(k)); CK(e->dTopId.reserve(k)); CK(e->dTopCount.reserve(1));
     CK(launch_topk(e->dCost.p, e->dFlags.p, n, e->lastFirst, k, e->dTopCost.p, e->dTopId.p,
                    e->dTopCount.p, e->dTopkScratch.p, e->dTopkScratch.cap, e->stream));
-    e->launches += 3;
+    e->launches += 4;
     return BCU_OK;
 }
 
@@ -662,8 +689,13 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
         }
         gathered = e->dBlockAll.p;
     }
-    CK(launch_merge_records(gathered, e->nRanks, k, e->nBalls, e->dBlockMerged.p, e->stream));
-    e->launches += 2;
+    if (e->nRanks > 1) {
+        CK(launch_merge_records(gathered, e->nRanks, k, e->nBalls, e->dBlockMerged.p, e->stream));
+        e->launches += 2;
+        e->beamBlock = e->dBlockMerged.p;
+    } else {
+        e->beamBlock = e->dBlockLocal.p;   // one rank: the packed local block is the beam
+    }
     e->beamK = k;
     e->haveBeam = true;
     return BCU_OK;  // asynchronous: bcu_fetch_beam / bcu_sync wait for it
@@ -684,17 +716,26 @@ int bcu_fetch_beam(bcu_engine* e, int32_t* outCount, uint64_t* outCost, uint64_t
     if (!e->haveBeam) return fail(e, BCU_ERR_STATE, "bcu_fetch_beam: no bcu_level_select yet");
     CK(cudaSetDevice(e->device));
     const int k = e->beamK, NB = e->nBalls;
-    char* base = (char*)e->dBlockMerged.p;
-    std::vector<uint64_t> ids(k);
-    CK(cudaMemcpyAsync(ids.data(), base + (size_t)k * 8, (size_t)k * 8, cudaMemcpyDeviceToHost, e->stream));
-    if (outCost) CK(cudaMemcpyAsync(outCost, base, (size_t)k * 8, cudaMemcpyDeviceToHost, e->stream));
-    if (outPotted) CK(cudaMemcpyAsync(outPotted, base + (size_t)k * 16, (size_t)k * 4, cudaMemcpyDeviceToHost, e->stream));
-    if (outTime) CK(cudaMemcpyAsync(outTime, base + (size_t)k * 20, (size_t)k * 4, cudaMemcpyDeviceToHost, e->stream));
-    if (outPos) CK(cudaMemcpyAsync(outPos, base + (size_t)k * 24, (size_t)k * NB * 8, cudaMemcpyDeviceToHost, e->stream));
+    // one copy of the whole record block into page-locked staging (the caller's arrays are usually pageable: five small
+    // copies into them would each be staged and synchronised by the driver), then plain host copies
+    const size_t bb = record_block_bytes(k, NB), need = outPos ? bb : (size_t)k * 24;
+    if (e->hBeamCap < bb) {
+        if (e->hBeam) cudaFreeHost(e->hBeam);
+        e->hBeam = nullptr; e->hBeamCap = 0;
+        CK(cudaMallocHost(&e->hBeam, bb));
+        e->hBeamCap = bb;
+    }
+    CK(cudaMemcpyAsync(e->hBeam, e->beamBlock, need, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    const char* base = (const char*)e->hBeam;
+    const uint64_t* ids = (const uint64_t*)(base + (size_t)k * 8);
     int cnt = 0;
     while (cnt < k && ids[cnt] != ~0ull) cnt++;
-    if (outId) std::memcpy(outId, ids.data(), (size_t)k * 8);
+    if (outCost) std::memcpy(outCost, base, (size_t)k * 8);
+    if (outId) std::memcpy(outId, ids, (size_t)k * 8);
+    if (outPotted) std::memcpy(outPotted, base + (size_t)k * 16, (size_t)k * 4);
+    if (outTime) std::memcpy(outTime, base + (size_t)k * 20, (size_t)k * 4);
+    if (outPos) std::memcpy(outPos, base + (size_t)k * 24, (size_t)k * NB * 8);
     *outCount = cnt;
     return BCU_OK;
 }

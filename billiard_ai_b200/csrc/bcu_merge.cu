@@ -61,49 +61,53 @@ cudaError_t launch_pack_records(const uint64_t* keyCost, const uint64_t* keyId, 
     return cudaGetLastError();
 }
 
-// One CTA: rank r's list is already sorted, so the global rank of entry (r, j) is
-//   sum over r' of #{ entries of r' that sort before it }  -- G binary searches per entry, no shared memory.
-__global__ void merge_records_kernel(const void* gathered, int G, int k, int NB, size_t blockBytes, void* out) {
+// One warp per gathered entry: rank r's list is already sorted, so the global rank of entry (r, j) is
+//   j + sum over r' != r of #{ entries of r' that sort before it }  -- G - 1 binary searches (every lane runs the same
+// search: no divergence), then the warp copies the record to its place.
+__global__ void __launch_bounds__(256) merge_records_kernel(const void* gathered, int G, int k, int NB, size_t blockBytes,
+                                                            void* out) {
     BlockView o = view_block(out, k);
-    for (int e = threadIdx.x; e < G * k; e += blockDim.x) {
-        const int r = e / k, j = e - r * k;
-        BlockView mine = view_block((char*)gathered + (size_t)r * blockBytes, k);
-        const uint64_t c = mine.cost[j], id = mine.id[j];
-        if (id == ~0ull) continue;  // padding
-        int rank = j;
-        for (int q = 0; q < G; ++q) {
-            if (q == r) continue;
-            BlockView other = view_block((char*)gathered + (size_t)q * blockBytes, k);
-            int lo = 0, hi = k;  // first index whose key is not < (c, id)
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                const uint64_t oc = other.cost[mid], oi = other.id[mid];
-                const bool less = oc < c || (oc == c && oi < id);
-                if (less) lo = mid + 1; else hi = mid;
-            }
-            rank += lo;
+    const int lane = threadIdx.x & 31;
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= G * k) return;
+    const int r = e / k, j = e - r * k;
+    BlockView mine = view_block((char*)gathered + (size_t)r * blockBytes, k);
+    const uint64_t c = mine.cost[j], id = mine.id[j];
+    if (id == ~0ull) return;  // padding
+    int rank = j;
+    for (int q = 0; q < G && rank < k; ++q) {
+        if (q == r) continue;
+        BlockView other = view_block((char*)gathered + (size_t)q * blockBytes, k);
+        int lo = 0, hi = k;  // first index whose key is not < (c, id)
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            const uint64_t oc = other.cost[mid], oi = other.id[mid];
+            const bool less = oc < c || (oc == c && oi < id);
+            if (less) lo = mid + 1; else hi = mid;
         }
-        if (rank < k) {
-            o.cost[rank] = c;
-            o.id[rank] = id;
-            o.potted[rank] = mine.potted[j];
-            o.time[rank] = mine.time[j];
-            for (int i = 0; i < NB * 2; ++i) o.pos[(size_t)rank * NB * 2 + i] = mine.pos[(size_t)j * NB * 2 + i];
-        }
+        rank += lo;
     }
+    if (rank >= k) return;
+    if (lane == 0) {
+        o.cost[rank] = c;
+        o.id[rank] = id;
+        o.potted[rank] = mine.potted[j];
+        o.time[rank] = mine.time[j];
+    }
+    for (int i = lane; i < NB * 2; i += 32) o.pos[(size_t)rank * NB * 2 + i] = mine.pos[(size_t)j * NB * 2 + i];
 }
 
-__global__ void fill_block_kernel(void* out, int k, int NB) {
+// padding for the slots the merge leaves untouched (fewer than k valid entries over all ranks)
+__global__ void __launch_bounds__(256) fill_block_kernel(void* out, int k, int NB) {
     BlockView o = view_block(out, k);
-    for (int j = threadIdx.x + blockIdx.x * blockDim.x; j < k; j += blockDim.x * gridDim.x) {
-        o.cost[j] = ~0ull; o.id[j] = ~0ull; o.potted[j] = 0u; o.time[j] = 0.0f;
-        for (int i = 0; i < NB * 2; ++i) o.pos[(size_t)j * NB * 2 + i] = 0.0f;
-    }
+    const int t = threadIdx.x + blockIdx.x * blockDim.x, step = blockDim.x * gridDim.x;
+    for (int j = t; j < k; j += step) { o.cost[j] = ~0ull; o.id[j] = ~0ull; o.potted[j] = 0u; o.time[j] = 0.0f; }
+    for (int i = t; i < k * NB * 2; i += step) o.pos[i] = 0.0f;
 }
 
 cudaError_t launch_merge_records(const void* gathered, int G, int k, int nBalls, void* out, cudaStream_t stream) {
-    fill_block_kernel<<<(k + 255) / 256, 256, 0, stream>>>(out, k, nBalls);
-    merge_records_kernel<<<1, 1024, 0, stream>>>(gathered, G, k, nBalls, record_block_bytes(k, nBalls), out);
+    fill_block_kernel<<<(k * nBalls * 2 + 255) / 256, 256, 0, stream>>>(out, k, nBalls);
+    merge_records_kernel<<<(G * k + 7) / 8, 256, 0, stream>>>(gathered, G, k, nBalls, record_block_bytes(k, nBalls), out);
     return cudaGetLastError();
 }
 

@@ -4,8 +4,14 @@
 // SearchNode::_cost, type.hpp:572); ties are broken here by the global candidate id so that the
 // selection is deterministic and identical on every rank.
 //
-// Pass 1 (topk_select): each CTA compacts the valid keys of its slice into a 2048-entry bitonic sorter in shared memory,
-// keeping a running best-1024.  Pass 2 (topk_rank_merge): the sorted per-CTA lists are merged by rank.
+// Valid strikes are a small share of a level, so the selection works on a compacted list:
+//   topk_compact     every valid (cost, id) is appended to one global list (one atomicAdd per warp); V = their number.
+//   topk_rank_small  V <= TK_LIST: the rank of a key is the number of keys that sort before it -- V * V comparisons spread
+//                    over the grid (a warp per key), keys of rank < k scattered straight to their place.  No sort.
+//   V > TK_LIST (dense levels): the streaming sorter below.  Pass 1 (topk_select): each CTA compacts the valid keys of
+//   its slice into a 2048-entry bitonic sorter in shared memory, keeping a running best-1024.  Pass 2 (topk_rank_merge):
+//   the sorted per-CTA lists are merged by rank.
+// All four kernels are launched every time; the pair that does not apply reads V and returns (the host never syncs).
 #include <cuda_runtime.h>
 
 #include "bcu_kernels.cuh"
@@ -14,6 +20,8 @@ namespace bcu {
 
 constexpr int TK_THREADS = 1024;
 constexpr int TK_CAP = 1024;  // max k
+constexpr int TK_LIST = 16384;  // compacted list: above this many valid keys the streaming sorter takes over
+constexpr int TK_LANES = 32;    // lanes that share the comparisons of one key in topk_rank_small (a warp per key)
 
 struct Key {
     uint64_t cost, id;
@@ -38,12 +46,68 @@ __device__ void bitonic_sort_2048(uint64_t* sc, uint64_t* si) {
     __syncthreads();
 }
 
+// Compaction of the valid keys (order within the list is irrelevant: ranks come from the keys).  *outValid counts every
+// valid key, also those beyond the list's capacity.  The first k threads pre-fill the output with padding.
+__global__ void __launch_bounds__(256) topk_compact(const uint64_t* __restrict__ inCost, const uint32_t* __restrict__ inFlags,
+                                                    int64_t n, int64_t firstCandidate, int k, ulonglong2* __restrict__ list,
+                                                    int32_t* outValid, uint64_t* outCost, uint64_t* outId) {
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t0 < k) { outCost[t0] = ~0ull; outId[t0] = ~0ull; }
+    const int lane = threadIdx.x & 31;
+    const int64_t step = (int64_t)gridDim.x * blockDim.x;
+    const int64_t nRound = (n + 31) & ~(int64_t)31;   // whole warps stay in the loop together
+    for (int64_t i = t0; i < nRound; i += step) {
+        const bool valid = i < n && (inFlags[i] & F_VALID);
+        const unsigned m = __ballot_sync(0xffffffffu, valid);
+        if (m == 0) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(outValid, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (valid) {
+            const int at = base + __popc(m & ((1u << lane) - 1u));
+            if (at < TK_LIST) list[at] = make_ulonglong2(inCost[i], (uint64_t)(firstCandidate + i));
+        }
+    }
+}
+
+// Rank by counting.  Keys are distinct (the id is unique), so rank(key) = #{keys that sort before it}.  A warp shares
+// one key and strides through the list together (32 consecutive entries per step, L1 / L2 resident); the kernel is
+// bound by load latency, so it runs one key per warp with the SMs full of warps rather than fewer, longer threads.
+__global__ void __launch_bounds__(256) topk_rank_small(const ulonglong2* __restrict__ list, const int32_t* __restrict__ nValid,
+                                                       int k, uint64_t* outCost, uint64_t* outId) {
+    const int V = *nValid;
+    if (V > TK_LIST) return;                           // the streaming sorter handles this level
+    const int e = (blockIdx.x * blockDim.x + threadIdx.x) / TK_LANES;
+    const int q = threadIdx.x & (TK_LANES - 1);
+    if ((int)(blockIdx.x * blockDim.x / TK_LANES) >= V) return;
+    const bool live = e < V;
+    const ulonglong2 me = live ? list[e] : make_ulonglong2(0ull, 0ull);
+    const unsigned __int128 mine = ((unsigned __int128)me.x << 64) | me.y;
+    int rank = 0;
+    int j = q;
+    for (; j + 3 * TK_LANES < V; j += 4 * TK_LANES) {
+        const ulonglong2 a = list[j], b = list[j + TK_LANES], c = list[j + 2 * TK_LANES], d = list[j + 3 * TK_LANES];
+        rank += ((((unsigned __int128)a.x << 64) | a.y) < mine) ? 1 : 0;
+        rank += ((((unsigned __int128)b.x << 64) | b.y) < mine) ? 1 : 0;
+        rank += ((((unsigned __int128)c.x << 64) | c.y) < mine) ? 1 : 0;
+        rank += ((((unsigned __int128)d.x << 64) | d.y) < mine) ? 1 : 0;
+    }
+    for (; j < V; j += TK_LANES) {
+        const ulonglong2 a = list[j];
+        rank += ((((unsigned __int128)a.x << 64) | a.y) < mine) ? 1 : 0;
+    }
+    #pragma unroll
+    for (int s = 1; s < TK_LANES; s <<= 1) rank += __shfl_xor_sync(0xffffffffu, rank, s);
+    if (live && q == 0 && rank < k) { outCost[rank] = me.x; outId[rank] = me.y; }
+}
+
 // Pass 1.  Each CTA streams its slice of the candidates: VALID keys are compacted (ballot + prefix) into the upper half
 // of the 2048-entry sorter, and only when that half could overflow (or at the end) the sorter runs, leaving the running
 // best-1024 in the lower half.  With the usual few-percent share of valid strikes a CTA sorts once.
 __global__ void __launch_bounds__(TK_THREADS) topk_select(const uint64_t* inCost, const uint32_t* inFlags, int64_t n,
                                                           int64_t firstCandidate, int k, uint64_t* outCost, uint64_t* outId,
-                                                          int32_t* outValid) {
+                                                          const int32_t* nValid) {
+    if (*nValid <= TK_LIST) return;                    // topk_rank_small has done this level
     __shared__ uint64_t sc[2 * TK_CAP];
     __shared__ uint64_t si[2 * TK_CAP];
     __shared__ int sWarp[TK_THREADS / 32];
@@ -53,7 +117,7 @@ __global__ void __launch_bounds__(TK_THREADS) topk_select(const uint64_t* inCost
     const int64_t per = (n + gridDim.x - 1) / gridDim.x;
     const int64_t lo = per * blockIdx.x;
     const int64_t hi = lo + per < n ? lo + per : n;
-    int staged = 0, totalValid = 0;   // block-uniform
+    int staged = 0;   // block-uniform
     for (int64_t base = lo; base < hi; base += TK_CAP) {
         const int64_t i = base + tid;
         const bool valid = i < hi && (inFlags[i] & F_VALID);
@@ -73,12 +137,11 @@ __global__ void __launch_bounds__(TK_THREADS) topk_select(const uint64_t* inCost
             const int at = TK_CAP + staged + before + __popc(m & ((1u << lane) - 1u));
             sc[at] = inCost[i]; si[at] = (uint64_t)(firstCandidate + i);
         }
-        staged += cnt; totalValid += cnt;
+        staged += cnt;
         __syncthreads();
     }
     if (staged > 0) bitonic_sort_2048(sc, si);
     __syncthreads();
-    if (tid == 0 && totalValid && outValid) atomicAdd(outValid, totalValid);
     if (tid < k) { outCost[(int64_t)blockIdx.x * k + tid] = sc[tid]; outId[(int64_t)blockIdx.x * k + tid] = si[tid]; }
 }
 
@@ -86,7 +149,8 @@ __global__ void __launch_bounds__(TK_THREADS) topk_select(const uint64_t* inCost
 // its own index plus, for every other list, the number of entries that sort before it: L binary searches per entry,
 // spread over the whole grid; entries of rank < k are scattered to their place.
 __global__ void __launch_bounds__(256) topk_rank_merge(const uint64_t* partCost, const uint64_t* partId, int lists, int k,
-                                                       uint64_t* outCost, uint64_t* outId) {
+                                                       uint64_t* outCost, uint64_t* outId, const int32_t* nValid) {
+    if (*nValid <= TK_LIST) return;
     const int64_t total = (int64_t)lists * k;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
         const int r = (int)(e / k), j = (int)(e - (int64_t)r * k);
@@ -108,11 +172,6 @@ __global__ void __launch_bounds__(256) topk_rank_merge(const uint64_t* partCost,
     }
 }
 
-__global__ void topk_fill(uint64_t* outCost, uint64_t* outId, int k) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < k) { outCost[i] = ~0ull; outId[i] = ~0ull; }
-}
-
 static int topk_ctas(int64_t nCand) {
     // few, long slices: valid keys are compacted before they reach the sorter, so a CTA usually sorts once however many
     // candidates it streams, and the rank merge costs (lists - 1) dependent binary searches per entry
@@ -122,7 +181,9 @@ static int topk_ctas(int64_t nCand) {
     return (int)c;
 }
 
-size_t topk_scratch_bytes(int64_t nCand, int k) { return (size_t)topk_ctas(nCand) * k * 2 * sizeof(uint64_t) + 16; }
+size_t topk_scratch_bytes(int64_t nCand, int k) {
+    return (size_t)TK_LIST * sizeof(ulonglong2) + (size_t)topk_ctas(nCand) * k * 2 * sizeof(uint64_t) + 16;
+}
 
 cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCand, int64_t firstCandidate, int k,
                         uint64_t* outKeyCost, uint64_t* outKeyId, int32_t* outCount, void* scratch, size_t scratchBytes,
@@ -130,13 +191,18 @@ cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCa
     if (k < 1 || k > TK_CAP) return cudaErrorInvalidValue;
     const int ctas = topk_ctas(nCand);
     if (scratchBytes < topk_scratch_bytes(nCand, k)) return cudaErrorInvalidValue;
-    uint64_t* partCost = reinterpret_cast<uint64_t*>(scratch);
+    ulonglong2* list = reinterpret_cast<ulonglong2*>(scratch);
+    uint64_t* partCost = reinterpret_cast<uint64_t*>(list + TK_LIST);
     uint64_t* partId = partCost + (size_t)ctas * k;
     cudaMemsetAsync(outCount, 0, sizeof(int32_t), stream);
+    int64_t cc = (nCand + 1023) / 1024;   // 4 candidates per thread at least, one wave at most
+    if (cc < (k + 255) / 256) cc = (k + 255) / 256;
+    if (cc > 148 * 4) cc = 148 * 4;
+    topk_compact<<<(unsigned)cc, 256, 0, stream>>>(cost, flags, nCand, firstCandidate, k, list, outCount, outKeyCost, outKeyId);
+    topk_rank_small<<<TK_LIST * TK_LANES / 256, 256, 0, stream>>>(list, outCount, k, outKeyCost, outKeyId);
     topk_select<<<ctas, TK_THREADS, 0, stream>>>(cost, flags, nCand, firstCandidate, k, partCost, partId, outCount);
-    topk_fill<<<(k + 255) / 256, 256, 0, stream>>>(outKeyCost, outKeyId, k);
     const int64_t total = (int64_t)ctas * k;
-    topk_rank_merge<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(partCost, partId, ctas, k, outKeyCost, outKeyId);
+    topk_rank_merge<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(partCost, partId, ctas, k, outKeyCost, outKeyId, outCount);
     return cudaGetLastError();
 }
 

@@ -433,3 +433,31 @@ def test_launch_larger_than_one_pipeline_pass(engine):
         part = engine.fetch()
         for key in RESULT_KEYS:
             assert np.array_equal(part[key], full[off][key]), (off, key)
+
+
+def test_topk_dense_level_takes_the_streaming_sorter(engine):
+    """The selection has two device paths (bcu_topk.cu): rank-by-counting on the compacted list of valid strikes, and the
+    streaming sorter + rank merge when more than 16384 strikes are valid.  A 786k-strike level (48 states) has enough
+    valid strikes for the second; a 16k-strike slice of it runs the first.  Both must equal numpy's stable (cost, id) order."""
+    from billiard_ai_b200 import workloads as W
+    layouts = [W.random_layout(16, 16 + s) for s in range(48)]
+    spos = np.stack([p for p, _ in layouts]); stypes = np.stack([t for _, t in layouts])
+    base = (np.arange(48, dtype=np.uint64) * 3) % 11
+    engine.set_states(spos, stypes, 0xFE, base)            # any object ball counts: many valid strikes
+    dirs, speeds = W.grid(256, 64)
+    total = engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    res = engine.fetch(final_pos=False)
+    ids = np.nonzero((res["flags"] & F_VALID) != 0)[0]
+    assert len(ids) > 16384, len(ids)
+    order = ids[np.lexsort((ids, res["cost"][ids]))]
+    for k in (1, 100, 1024):
+        tc, ti = engine.topk(k)
+        assert np.array_equal(ti, order[:k].astype(np.uint64)) and np.array_equal(tc, res["cost"][order[:k]])
+    lo, n = 300000, 16384
+    engine.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=lo, count=n)
+    sel = ids[(ids >= lo) & (ids < lo + n)]
+    assert 0 < len(sel) <= 16384
+    o2 = sel[np.lexsort((sel, res["cost"][sel]))]
+    tc, ti = engine.topk(1024)
+    kk = min(1024, len(sel))
+    assert np.array_equal(ti, o2[:kk].astype(np.uint64)) and np.array_equal(tc, res["cost"][o2[:kk]])
