@@ -79,6 +79,42 @@ def _null(t):
     return C.POINTER(t)()
 
 
+class _LazyResults(dict):
+    """Per-strike results; "flags" (status bits) and "n_events" are unpacked from the raw flag words on first use."""
+
+    def __missing__(self, key):
+        if key == "flags":
+            v = self["flags_raw"] & 0xff
+        elif key == "n_events":
+            v = ((self["flags_raw"] >> 8) & 0xff).astype(np.int32)
+        else:
+            raise KeyError(key)
+        self[key] = v
+        return v
+
+    def _all(self):
+        self["flags"]; self["n_events"]
+        return self
+
+    def keys(self):
+        return dict.keys(self._all())
+
+    def items(self):
+        return dict.items(self._all())
+
+    def values(self):
+        return dict.values(self._all())
+
+    def __iter__(self):
+        return dict.__iter__(self._all())
+
+    def __contains__(self, key):
+        return key in ("flags", "n_events") or dict.__contains__(self, key)
+
+    def get(self, key, default=None):
+        return self[key] if key in self else default
+
+
 class Engine:
     """One engine = one CUDA device + one stream + the table / rules constants."""
 
@@ -188,9 +224,9 @@ class Engine:
 
     @staticmethod
     def _finish(out):
-        out["n_events"] = ((out["flags"] >> 8) & 0xff).astype(np.int32)
-        out["flags"] = out["flags"] & 0xff
-        return out
+        res = _LazyResults(out)
+        res["flags_raw"] = res.pop("flags")   # status bits 0-7, number of events bits 8-15 (include/billiard_cuda.h)
+        return res
 
     def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False, reuse_buffers=False):
         """reuse_buffers=True returns views of cached page-locked result buffers (overwritten by the next such call)."""
