@@ -638,6 +638,44 @@ int bcu_simulate_trace(bcu_engine* e, int32_t nBalls, const float* pos, const in
     return BCU_OK;
 }
 
+int bcu_trace_strikes(bcu_engine* e, int32_t n, const int32_t* stateIdx, const float* vx, const float* vy,
+                      int32_t* outLayers, float* outTimes, float* outRec) {
+    if (!e) return BCU_ERR_INVALID;
+    if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_trace_strikes: call bcu_set_states first");
+    if (n < 0 || n > 65536 || (n > 0 && (!stateIdx || !vx || !vy || !outLayers || !outTimes || !outRec)))
+        return fail(e, BCU_ERR_INVALID, "bcu_trace_strikes: bad arguments");
+    if (n == 0) return BCU_OK;
+    for (int32_t i = 0; i < n; ++i)
+        if (stateIdx[i] < 0 || stateIdx[i] >= e->nStates) return fail(e, BCU_ERR_INVALID, "bcu_trace_strikes: state index out of range");
+    CK(cudaSetDevice(e->device));
+    const int NB = e->nBalls;
+    const size_t recPer = (size_t)BCU_MAX_LAYERS * NB * BCU_TRACE_REC;
+    CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n)); CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
+    int rc = reserve_results(e, n, true, false);
+    if (rc) return rc;
+    CK(e->dTraceTimes.reserve((size_t)n * BCU_MAX_LAYERS)); CK(e->dTraceRec.reserve((size_t)n * recPer));
+    CK(cudaMemcpyAsync(e->dCandState.p, stateIdx, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVx.p, vx, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dVy.p, vy, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemsetAsync(e->dSearchCost.p, 0, (size_t)n * sizeof(uint64_t), e->stream));
+    CK(cudaMemsetAsync(e->dBaseCost.p, 0, (size_t)n * sizeof(uint64_t), e->stream));
+    LaunchParams p;
+    fill_common(e, p, n, true, false);
+    p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
+    p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
+    p.out.traceTimes = e->dTraceTimes.p; p.out.traceRec = e->dTraceRec.p;
+    rc = run(e, p, true);
+    if (rc) return rc;
+    std::vector<uint32_t> flags(n);
+    CK(cudaMemcpyAsync(flags.data(), e->dFlags.p, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(outTimes, e->dTraceTimes.p, (size_t)n * BCU_MAX_LAYERS * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(outRec, e->dTraceRec.p, (size_t)n * recPer * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->haveLast = false;   // the per-strike result arrays now hold the traced strikes (the beam records are untouched)
+    for (int32_t i = 0; i < n; ++i) outLayers[i] = (flags[i] & BCU_F_COMPLETED) ? (int32_t)BCU_N_EVENTS(flags[i]) + 1 : 0;
+    return BCU_OK;
+}
+
 int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* outPos, uint32_t* outPotted, float* outTime) {
     if (!e) return BCU_ERR_INVALID;
     if (!e->haveLast || !e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "bcu_gather: no launch with final positions");

@@ -141,9 +141,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) simulate_candidates(Launch
         uint32_t flags = 0;
 
         if (TRACE) {
-            if (lane == 0) p.out.traceTimes[0] = T;
+            if (lane == 0) p.out.traceTimes[cand * 32] = T;
             if (lane < NB) {
-                float* r = p.out.traceRec + (size_t)lane * 10;
+                float* r = p.out.traceRec + ((size_t)cand * 32 * NB + lane) * 10;
                 r[0] = kind == K_ABSENT ? -1.f : (float)kind; r[1] = pos.x; r[2] = pos.y; r[3] = vel.x; r[4] = vel.y;
                 r[5] = rolling ? 1.f : 0.f; r[6] = velBefore.x; r[7] = velBefore.y; r[8] = (float)cause; r[9] = -1.f;
                 if (kind == K_ABSENT) for (int k = 1; k < 10; ++k) r[k] = -1.f;
@@ -318,9 +318,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) simulate_candidates(Launch
                 p.out.eventLog[cand * 32 + (nEvents - 1)] = make_int4(evType, a, b, __float_as_int(T));
             }
             if (TRACE) {
-                if (lane == 0) p.out.traceTimes[nEvents] = T;
+                if (lane == 0) p.out.traceTimes[cand * 32 + nEvents] = T;
                 if (lane < NB) {
-                    float* r = p.out.traceRec + ((size_t)nEvents * NB + lane) * 10;
+                    float* r = p.out.traceRec + (((size_t)cand * 32 + nEvents) * NB + lane) * 10;
                     r[0] = (float)kind; r[1] = pos.x; r[2] = pos.y; r[3] = vel.x; r[4] = vel.y;
                     r[5] = rolling ? 1.f : 0.f; r[6] = velBefore.x; r[7] = velBefore.y; r[8] = (float)cause; r[9] = -1.f;
                     if (kind == K_ABSENT) for (int k = 0; k < 10; ++k) r[k] = -1.f;
@@ -379,10 +379,11 @@ void upload_constants(cudaStream_t stream) {
     cudaStreamSynchronize(stream);
 }
 
-// The single-strike trace (bcu_simulate_trace): one warp, full per-layer records.
+// The traced strikes (bcu_simulate_trace, bcu_trace_strikes): one warp per strike, full per-layer records.
 cudaError_t launch_trace(const LaunchParams& p, cudaStream_t stream) {
     if (p.nCand <= 0) return cudaSuccess;
-    simulate_candidates<true><<<1, WARPS_PER_CTA * 32, 0, stream>>>(p);
+    const int64_t ctas = (p.nCand + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
+    simulate_candidates<true><<<(unsigned)(ctas < 148 * 8 ? ctas : 148 * 8), WARPS_PER_CTA * 32, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -38,9 +38,9 @@ struct Results {
     float* finalTime;
     float* finalPos;      // [nCand][nBalls][2]  (may be null)
     int4* eventLog;       // [nCand][32] {type, a, b, layer time bits} (may be null)
-    // single-candidate trace (bcu_simulate_trace): per layer, per ball 10 floats as oracle/ref_driver.cpp
-    float* traceTimes;    // [32]
-    float* traceRec;      // [32][nBalls][10]
+    // traced strikes (bcu_simulate_trace, bcu_trace_strikes): per layer, per ball 10 floats as oracle/ref_driver.cpp
+    float* traceTimes;    // [nCand][32]
+    float* traceRec;      // [nCand][32][nBalls][10]
     // work counters (may be null): [0] events [1] pair items [2] quartics [3] rail items [4] pocket items
     unsigned long long* counters;
 };

@@ -350,6 +350,21 @@ class Engine:
         self.n_states, self.n_balls = 1, n
         return nl.value, times[:nl.value], rec[:nl.value]
 
+    def trace_strikes(self, cand_state, vx, vy):
+        """Full per-layer traces of n strikes on the current states -> (layers [n], times [n][32], rec [n][32][balls][10]);
+        layers[i] == 0 where the reference's simulate() would return nullopt."""
+        vx = np.ascontiguousarray(vx, dtype=np.float32)
+        vy = np.ascontiguousarray(vy, dtype=np.float32)
+        n = len(vx)
+        cs = np.ascontiguousarray(np.broadcast_to(np.asarray(cand_state, dtype=np.int32), (n,)))
+        layers = np.zeros(n, np.int32)
+        times = np.zeros((n, MAX_LAYERS), np.float32)
+        rec = np.zeros((n, MAX_LAYERS, self.n_balls, TRACE_REC), np.float32)
+        self._ck(self.lib.bcu_trace_strikes(self.h, C.c_int32(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
+                                            _p(layers, C.c_int32), _p(times, C.c_float), _p(rec, C.c_float)),
+                 "bcu_trace_strikes")
+        return layers, times, rec
+
     # ---- measurement hooks ------------------------------------------------------------------------
     def last_kernel_ms(self):
         ms = C.c_float(0)

@@ -25,6 +25,7 @@
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 #include "billiard_cuda.h"
@@ -101,6 +102,39 @@ public:
         int32_t layers = 0;
         check(bcu_simulate_trace(_e, n, pos.data(), types.data(), velocity.x, velocity.y, &layers, times.data(), rec.data()),
               "bcu_simulate_trace");
+        return systemFromTrace(state, layers, times.data(), rec.data());
+    }
+
+    // The strikes of several solutions at once -- one node::System per (state, velocity) pair, as the inner vectors of
+    // billiard::search::search()'s result hold one System per break (billiard_search.hpp:9-12, type.hpp:525-537).
+    // All states must have the same number of balls (the frame's slots; one launch, one copy back).
+    std::vector<std::optional<node::System>> simulateAll(const std::vector<State>& states,
+                                                         const std::vector<std::pair<int, glm::vec2>>& strikes) {
+        std::vector<std::optional<node::System>> out;
+        if (states.empty() || strikes.empty()) return out;
+        const int n = (int)states[0]._balls.size();
+        std::vector<float> pos;
+        std::vector<int32_t> types;
+        for (auto& st : states) {
+            if ((int)st._balls.size() != n) throw std::runtime_error("billiard::search::cuda: states of different sizes in one batch");
+            flatten(st, pos, types);
+        }
+        std::vector<uint32_t> mask(states.size(), 0xffffffffu);
+        check(bcu_set_states(_e, (int32_t)states.size(), n, pos.data(), types.data(), mask.data(), nullptr), "bcu_set_states");
+        const int32_t m = (int32_t)strikes.size();
+        std::vector<int32_t> sidx(m), layers(m);
+        std::vector<float> vx(m), vy(m), times((size_t)m * BCU_MAX_LAYERS), rec((size_t)m * BCU_MAX_LAYERS * n * BCU_TRACE_REC);
+        for (int32_t i = 0; i < m; ++i) { sidx[i] = strikes[i].first; vx[i] = strikes[i].second.x; vy[i] = strikes[i].second.y; }
+        check(bcu_trace_strikes(_e, m, sidx.data(), vx.data(), vy.data(), layers.data(), times.data(), rec.data()), "bcu_trace_strikes");
+        for (int32_t i = 0; i < m; ++i)
+            out.push_back(systemFromTrace(states[sidx[i]], layers[i], &times[(size_t)i * BCU_MAX_LAYERS],
+                                          &rec[(size_t)i * BCU_MAX_LAYERS * n * BCU_TRACE_REC]));
+        return out;
+    }
+
+    // device trace (include/billiard_cuda.h: bcu_simulate_trace) -> the reference's node::System
+    std::optional<node::System> systemFromTrace(const State& state, int layers, const float* times, const float* rec) {
+        const int n = (int)state._balls.size();
         if (layers == 0) return std::nullopt;  // billiard_search.cpp:170-174
         const float al = physics::accelerationLength(), sl = physics::slideAccelerationLength();
         node::System system;

@@ -29,8 +29,8 @@ def _mask_of(type_codes):
 def search_levels(engine, pos, types, search_types, levels, beam, dirs, speeds, rules, search_cost=GRID_SEARCH_COST,
                   rank=0, world=1, stats=None):
     """-> solutions, ascending by (cost, discovery order): dicts with `cost`, `strikes` (one (vx, vy) per break),
-    `dirs` / `speeds` (grid indices per break), `pos` / `present` (table after the last break, rules applied when a
-    further break was seeded) and `breaks`.
+    `dirs` / `speeds` (grid indices per break), `frames` (the (pos, types) frame each break was played on), `pos` /
+    `present` (table after the last break, rules applied when a further break was seeded) and `breaks`.
 
     pos, types: the frame (types < 0: no ball in that slot).  search_types: type codes the first break may pot.
     `stats`, if given, receives per-level dicts (states, candidates, beam entries, ms of device time)."""
@@ -64,12 +64,12 @@ def search_levels(engine, pos, types, search_types, levels, beam, dirs, speeds, 
             k, j = divmod(rem, n_speeds)
             parent = states[si]
             vx = np.float32(speeds[j] * dirs[k, 0]); vy = np.float32(speeds[j] * dirs[k, 1])
-            path = parent["path"] + [(k, j, float(vx), float(vy))]
+            path = parent["path"] + [(k, j, float(vx), float(vy), parent["pos"], parent["types"])]
             frame_types = parent["types"]
             present = ((frame_types >= 0) & (((potted >> np.arange(len(frame_types))) & 1) == 0)).astype(np.uint8)
             rest_pos = np.where(present[:, None].astype(bool), fpos, 0.0).astype(np.float32)
             sol = dict(cost=int(cost), breaks=level + 1, strikes=[(p[2], p[3]) for p in path], dirs=[p[0] for p in path],
-                       speeds=[p[1] for p in path], pos=rest_pos, present=present)
+                       speeds=[p[1] for p in path], frames=[(p[4], p[5]) for p in path], pos=rest_pos, present=present)
             if level + 1 >= levels:                                         # simCount == BREAKS (:1407)
                 solutions.append(sol)
                 continue
@@ -88,3 +88,32 @@ def search_levels(engine, pos, types, search_types, levels, beam, dirs, speeds, 
         states = nxt
     solutions.sort(key=lambda s: s["cost"])   # stable: equal costs stay in discovery order
     return solutions
+
+
+def solution_traces(engine, solutions, top=None):
+    """Full per-layer traces of every break of the first `top` solutions -- what billiard::search::search() returns as one
+    node::System per break of each solution (billiard_search.hpp:9-12; SURVEY.md 8f-1) -- in ONE device call
+    (bcu_trace_strikes).  -> per solution a list, per break a dict `layers`, `times [layers]`, `rec [layers][balls][10]`
+    (record layout: include/billiard_cuda.h, bcu_simulate_trace)."""
+    sols = solutions if top is None else solutions[:top]
+    if not sols:
+        return []
+    frames, slot, sidx, vx, vy = [], {}, [], [], []
+    for s in sols:
+        for (fpos, ftypes), (svx, svy) in zip(s["frames"], s["strikes"]):
+            key = id(fpos)
+            if key not in slot:
+                slot[key] = len(frames)
+                frames.append((fpos, ftypes))
+            sidx.append(slot[key]); vx.append(svx); vy.append(svy)
+    engine.set_states(np.stack([f[0] for f in frames]), np.stack([f[1] for f in frames]), 0xFFFFFFFF)
+    layers, times, rec = engine.trace_strikes(np.array(sidx, np.int32), np.array(vx, np.float32), np.array(vy, np.float32))
+    out, i = [], 0
+    for s in sols:
+        per = []
+        for _ in s["strikes"]:
+            n = int(layers[i])
+            per.append(dict(layers=n, times=times[i, :n].copy(), rec=rec[i, :n].copy()))
+            i += 1
+        out.append(per)
+    return out

@@ -134,6 +134,14 @@ int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* out_pos, ui
 int bcu_simulate_trace(bcu_engine* e, int32_t n_balls, const float* pos, const int32_t* types, float vx, float vy,
                        int32_t* out_layers, float* out_times, float* out_rec);
 
+/* The same for n strikes at once on the states of the last bcu_set_states (the reference returns one node::System per
+ * break of every solution, billiard_search.hpp:9-12 / type.hpp:525-537: trace the strikes of the best solutions in one
+ * call).  state_idx / vx / vy [n], n <= 65536; out_layers [n] (0: the reference would return nullopt),
+ * out_times [n][32], out_rec [n][32][n_balls][10] as above.  Overwrites the per-strike results of the last launch
+ * (bcu_fetch_results / bcu_topk need a new launch afterwards); the beam of bcu_level_select stays valid. */
+int bcu_trace_strikes(bcu_engine* e, int32_t n, const int32_t* state_idx, const float* vx, const float* vy,
+                      int32_t* out_layers, float* out_times, float* out_rec);
+
 /* ---- one break level, device resident (billiard_search.cpp:224-244 expand + process.hpp:19-25 pop order) ----
  * After bcu_evaluate_grid: select the k best VALID candidates by (cost, id), pack their end states into a record
  * block, all-gather the blocks of all ranks (one ncclAllGather; skipped for a single rank) and merge them into

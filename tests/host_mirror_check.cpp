@@ -76,6 +76,16 @@ extern "C" int mirror_check(int n, const float* pos, const char* const* typeName
             compared++;
             if (compareSystems(*want, *got) != 0) bad++;
         }
+        // the same strikes in one batch (Engine::simulateAll -> bcu_trace_strikes), two copies of the state
+        std::vector<std::pair<int, glm::vec2>> strikes;
+        for (int s = 0; s < nStrikes; ++s) strikes.push_back({s & 1, glm::vec2{vx[s], vy[s]}});
+        auto all = engine.simulateAll({state, state}, strikes);
+        if ((int)all.size() != nStrikes) return -1;
+        for (int s = 0; s < nStrikes; ++s) {
+            auto want = simulate(state, strikes[s].second, conf);
+            if (want.has_value() != all[s].has_value()) { bad++; continue; }
+            if (want && compareSystems(*want, *all[s]) != 0) bad++;
+        }
         *outCompared = compared;
         *outNullopt = nullopts;
         return bad;

@@ -139,3 +139,36 @@ def test_config3_full_size_properties(engine):
     assert stats[2]["candidates"] >= 1_000_000
     print(stats)
     assert all(int(s["present"].sum()) <= 16 - 3 for s in a)   # one ball at least potted per break
+
+
+def test_solution_traces_of_a_three_break_search(engine):
+    """one trace per break of the best solutions in one call (bcu_trace_strikes).  Each must equal the
+    single-strike trace of the same frame and strike bit for bit (bcu_simulate_trace, which test_gpu_parity.py checks
+    against the reference's node::System), chain up (the balls at rest after break b are the frame of break b + 1 up to
+    the rules' re-spotting) and end in the solution's end state."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import SnookerRules
+    from billiard_ai_b200.search import search_levels, solution_traces
+    pos, types = W.snooker22_open(22)
+    dirs, speeds = W.grid(48, 6)
+    sols = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 24, dirs, speeds, SnookerRules())
+    deep = [s for s in sols if s["breaks"] == 3][:8]
+    assert deep
+    traces = solution_traces(engine, deep)
+    assert len(traces) == len(deep)
+    for s, per in zip(deep, traces):
+        assert len(per) == 3
+        for b, tr in enumerate(per):
+            fpos, ftypes = s["frames"][b]
+            nl, times, rec = engine.simulate_trace(fpos, ftypes, *s["strikes"][b])
+            assert tr["layers"] == nl > 1
+            assert np.array_equal(tr["times"].view(np.uint32), times.view(np.uint32))
+            assert np.array_equal(tr["rec"].view(np.uint32), rec.view(np.uint32))
+        last = per[-1]["rec"][-1]
+        on = s["present"].astype(bool)
+        assert np.array_equal(last[on, 1:3].view(np.uint32), s["pos"][on].view(np.uint32))   # end state of the solution
+        kinds = last[:, 0].astype(int)
+        assert all(kinds[i] in (W_KIND_REST, W_KIND_POTTING) for i in range(len(kinds)) if ftypes[i] >= 0)
+
+
+W_KIND_REST, W_KIND_POTTING = 5, 3
