@@ -112,18 +112,8 @@ BCU_HD void fb_sincos(double x, double* s, double* c) {
 
 // ---- exp -------------------------------------------------------------------------------------------------------
 // exp_inline of e_pow.c / the body of e_exp.c: exp(x + xtail) * (-1)^(sign_bias != 0); N = 128.
-BCU_HD double exp_core(double x, double xtail, bool withTail, uint64_t signBias, bool* ok) {
-    const uint32_t abstop = (uint32_t)(d2u(x) >> 52) & 0x7ff;
-    *ok = true;
-    if (abstop - 0x3c9u >= 0x3fu) {  // |x| < 2^-54 or |x| >= 512: special handling in glibc
-        if (abstop - 0x3c9u >= 0x80000000u) {
-            // tiny: exp(x) = 1 + x (e_exp.c) ; pow: +-1 (e_pow.c returns 1.0 + x only when rounding matters)
-            const double one = 1.0;
-            return signBias ? -(one + x) : one + x;
-        }
-        *ok = false;  // overflow / underflow / subnormal result paths
-        return 0.0;
-    }
+// the straight-line part of exp_core (2^-54 <= |x| < 512): no branches, so several calls interleave in one block
+BCU_HD double exp_core_body(double x, double xtail, bool withTail, uint64_t signBias) {
     const double InvLn2N = BCU_TABD(BCU_EXP_HEAD, 0), Shift = BCU_TABD(BCU_EXP_HEAD, 1);
     const double NegLn2hiN = BCU_TABD(BCU_EXP_HEAD, 2), NegLn2loN = BCU_TABD(BCU_EXP_HEAD, 3);
     const double C2 = BCU_TABD(BCU_EXP_HEAD, 4), C3 = BCU_TABD(BCU_EXP_HEAD, 5);
@@ -146,9 +136,23 @@ BCU_HD double exp_core(double x, double xtail, bool withTail, uint64_t signBias,
     double tmp = bcu_fma(p23, r2, tr);
     const double r4 = r2 * r2;
     tmp = bcu_fma(r4, p45, tmp);
-    if (abstop == 0) { *ok = false; return 0.0; }    // unreachable (handled above); keeps glibc's structure
     const double scale = u2d(sbits);
     return bcu_fma(scale, tmp, scale);               // scale + scale*tmp
+}
+
+BCU_HD double exp_core(double x, double xtail, bool withTail, uint64_t signBias, bool* ok) {
+    const uint32_t abstop = (uint32_t)(d2u(x) >> 52) & 0x7ff;
+    *ok = true;
+    if (abstop - 0x3c9u >= 0x3fu) {  // |x| < 2^-54 or |x| >= 512: special handling in glibc
+        if (abstop - 0x3c9u >= 0x80000000u) {
+            // tiny: exp(x) = 1 + x (e_exp.c) ; pow: +-1 (e_pow.c returns 1.0 + x only when rounding matters)
+            const double one = 1.0;
+            return signBias ? -(one + x) : one + x;
+        }
+        *ok = false;  // overflow / underflow / subnormal result paths
+        return 0.0;
+    }
+    return exp_core_body(x, xtail, withTail, signBias);
 }
 
 BCU_HD double g_exp(double x) {
@@ -235,32 +239,8 @@ BCU_HD int pow_checkint(uint64_t iy) {
     return 2;
 }
 
-BCU_HD double g_pow(double x, double y) {
-    uint64_t ix = d2u(x);
-    const uint64_t iy = d2u(y);
-    uint32_t topx = (uint32_t)(ix >> 52);
-    const uint32_t topy = (uint32_t)(iy >> 52);
-    uint64_t signBias = 0;
-    if (topx - 0x001u >= 0x7ffu - 0x001u || (topy & 0x7ff) - 0x3beu >= 0x43eu - 0x3beu) {
-        // e_pow.c special cases.  Restated: x = +-0 and finite negative normal x, both with a finite normal-range y
-        // (the quartic calls pow(b, 3) / pow(c, 3) with b, c of either sign or zero); the rest falls back.
-        if ((topy & 0x7ff) - 0x3beu >= 0x43eu - 0x3beu) return fb_pow(x, y);
-        if (2 * ix == 0) {
-            double x2 = x * x;
-            if ((ix >> 63) && pow_checkint(iy) == 1) x2 = -x2;
-            return (iy >> 63) ? 1 / x2 : x2;
-        }
-        if ((ix >> 63) && (topx & 0x7ff) - 0x001u < 0x7ffu - 0x001u) {
-            const int yint = pow_checkint(iy);
-            if (yint == 0) return fb_pow(x, y);           // invalid -> NaN
-            if (yint == 1) signBias = 0x800ULL << 7;      // SIGN_BIAS
-            ix &= 0x7fffffffffffffffULL;
-            topx &= 0x7ff;
-        } else {
-            return fb_pow(x, y);                          // subnormal, inf, nan
-        }
-    }
-    // log_inline
+// log_inline of e_pow.c for a positive normal ix: lhi + llo = log(x), straight-line
+BCU_HD void pow_log_part(uint64_t ix, double* outHi, double* outLo) {
     const uint64_t OFF = 0x3fe6955500000000ULL;
     const uint64_t tmp = ix - OFF;
     const uint32_t i = (uint32_t)(tmp >> 45) & 127;
@@ -296,6 +276,37 @@ BCU_HD double g_pow(double x, double y) {
     lo = bcu_fma(ar3, q, lo);
     const double lhi = hi + lo;
     const double llo = (hi - lhi) + lo;
+    *outHi = lhi;
+    *outLo = llo;
+}
+
+BCU_HD double g_pow(double x, double y) {
+    uint64_t ix = d2u(x);
+    const uint64_t iy = d2u(y);
+    uint32_t topx = (uint32_t)(ix >> 52);
+    const uint32_t topy = (uint32_t)(iy >> 52);
+    uint64_t signBias = 0;
+    if (topx - 0x001u >= 0x7ffu - 0x001u || (topy & 0x7ff) - 0x3beu >= 0x43eu - 0x3beu) {
+        // e_pow.c special cases.  Restated: x = +-0 and finite negative normal x, both with a finite normal-range y
+        // (the quartic calls pow(b, 3) / pow(c, 3) with b, c of either sign or zero); the rest falls back.
+        if ((topy & 0x7ff) - 0x3beu >= 0x43eu - 0x3beu) return fb_pow(x, y);
+        if (2 * ix == 0) {
+            double x2 = x * x;
+            if ((ix >> 63) && pow_checkint(iy) == 1) x2 = -x2;
+            return (iy >> 63) ? 1 / x2 : x2;
+        }
+        if ((ix >> 63) && (topx & 0x7ff) - 0x001u < 0x7ffu - 0x001u) {
+            const int yint = pow_checkint(iy);
+            if (yint == 0) return fb_pow(x, y);           // invalid -> NaN
+            if (yint == 1) signBias = 0x800ULL << 7;      // SIGN_BIAS
+            ix &= 0x7fffffffffffffffULL;
+            topx &= 0x7ff;
+        } else {
+            return fb_pow(x, y);                          // subnormal, inf, nan
+        }
+    }
+    double lhi, llo;
+    pow_log_part(ix, &lhi, &llo);
     // ehi + elo = y * (lhi + llo)
     const double ehi = y * lhi;
     double elo = bcu_fma(lhi, y, -ehi);
@@ -303,6 +314,36 @@ BCU_HD double g_pow(double x, double y) {
     bool ok;
     const double res = exp_core(ehi, elo, true, signBias, &ok);
     return ok ? res : fb_pow(x, y);
+}
+
+// pow(x0, 3.0), pow(x1, 3.0), pow(x2, 3.0) -- each exactly the operation sequence of g_pow, but the three chains sit in
+// one straight-line block so that the scheduler interleaves them (the quartic's b^3, a^3, c^3: a serial chain of three
+// pows is a tenth of the solver's latency).  Anything outside the ordinary range goes through g_pow one by one.
+BCU_HD void g_cubes3(double x0, double x1, double x2, double* r0, double* r1, double* r2) {
+    uint64_t i0 = d2u(x0), i1 = d2u(x1), i2 = d2u(x2);
+    const uint32_t e0 = (uint32_t)(i0 >> 52) & 0x7ff, e1 = (uint32_t)(i1 >> 52) & 0x7ff, e2 = (uint32_t)(i2 >> 52) & 0x7ff;
+    if (e0 - 1u < 0x7feu && e1 - 1u < 0x7feu && e2 - 1u < 0x7feu) {   // finite, normal, non-zero (either sign)
+        const uint64_t SIGN = 0x8000000000000000ULL, BIAS = 0x800ULL << 7;   // 3 is odd: SIGN_BIAS for a negative base
+        const uint64_t s0 = (i0 & SIGN) ? BIAS : 0, s1 = (i1 & SIGN) ? BIAS : 0, s2 = (i2 & SIGN) ? BIAS : 0;
+        i0 &= ~SIGN; i1 &= ~SIGN; i2 &= ~SIGN;
+        double h0, l0, h1, l1, h2, l2;
+        pow_log_part(i0, &h0, &l0);
+        pow_log_part(i1, &h1, &l1);
+        pow_log_part(i2, &h2, &l2);
+        const double y = 3.0;
+        const double eh0 = y * h0, eh1 = y * h1, eh2 = y * h2;
+        double el0 = bcu_fma(h0, y, -eh0), el1 = bcu_fma(h1, y, -eh1), el2 = bcu_fma(h2, y, -eh2);
+        el0 = bcu_fma(y, l0, el0); el1 = bcu_fma(y, l1, el1); el2 = bcu_fma(y, l2, el2);
+        const uint32_t a0 = (uint32_t)(d2u(eh0) >> 52) & 0x7ff, a1 = (uint32_t)(d2u(eh1) >> 52) & 0x7ff;
+        const uint32_t a2 = (uint32_t)(d2u(eh2) >> 52) & 0x7ff;
+        if (a0 - 0x3c9u < 0x3fu && a1 - 0x3c9u < 0x3fu && a2 - 0x3c9u < 0x3fu) {   // exp_core's ordinary range
+            *r0 = exp_core_body(eh0, el0, true, s0);
+            *r1 = exp_core_body(eh1, el1, true, s1);
+            *r2 = exp_core_body(eh2, el2, true, s2);
+            return;
+        }
+    }
+    *r0 = g_pow(x0, 3.0); *r1 = g_pow(x1, 3.0); *r2 = g_pow(x2, 3.0);
 }
 
 // ---- log1p -----------------------------------------------------------------------------------------------------

@@ -27,10 +27,12 @@ BCU_HD cplx quartic_S(cplx p, cplx Q, cplx deltaZero, double a) {
 BCU_HD int solve_quartic_roots(double a, double b, double c, double d, double e, cplx roots[4]) {
     if (a == 0.0) return 0;
 
+    double b3, a3, c3;   // std::pow(b, 3.0), std::pow(a, 3.0), std::pow(c, 3.0) (:484-487)
+    g_cubes3(b, a, c, &b3, &a3, &c3);
     cplx p = c_make(((8 * a * c) - (3 * b * b)) / (8 * a * a));
-    cplx q = c_make((g_pow(b, 3.0) - (4 * a * b * c) + (8 * a * a * d)) / (8 * g_pow(a, 3.0)));
+    cplx q = c_make((b3 - (4 * a * b * c) + (8 * a * a * d)) / (8 * a3));
     cplx deltaZero = c_make((c * c) - (3 * b * d) + (12 * a * e));
-    cplx deltaOne = c_make((2 * g_pow(c, 3.0)) - (9 * b * c * d) + (27 * b * b * e) + (27 * a * d * d) - (72 * a * c * e));
+    cplx deltaOne = c_make((2 * c3) - (9 * b * c * d) + (27 * b * b * e) + (27 * a * d * d) - (72 * a * c * e));
 
     // std::pow(complex, int 3) = __complex_pow_unsigned: y = x; x *= x; y *= x
     cplx dz2 = c_mul(deltaZero, deltaZero);
