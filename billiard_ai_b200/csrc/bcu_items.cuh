@@ -14,7 +14,10 @@
 //            stage 2  quantised coefficients (:326-337) -> quartic job in the global queue
 #pragma once
 
-constexpr int ITEM_BLOCK = 128;
+#ifndef ITEM_BLOCK_V
+#define ITEM_BLOCK_V 128
+#endif
+constexpr int ITEM_BLOCK = ITEM_BLOCK_V;
 #ifndef ITEM_MIN_BLOCKS
 #define ITEM_MIN_BLOCKS 6
 #endif
@@ -100,7 +103,11 @@ __device__ __forceinline__ float reach_ball(const Reach& r, float v, float a) {
 #endif
 constexpr float PRUNE_MIN_LEADING = PRUNE_MIN_LEADING_V;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
 constexpr float PRUNE_MIN_SIN_SQ = PRUNE_MIN_SIN_SQ_V;
-constexpr uint32_t JOB_MARK = 0x80000000u;   // audit: the bound would have skipped this job
+constexpr uint32_t JOB_MARK = 0x80000000u;
+#ifndef PARTNER_BATCH_V
+#define PARTNER_BATCH_V 11
+#endif
+constexpr int PARTNER_BATCH = PARTNER_BATCH_V;   // resting partners loaded per memory round trip (22 balls: two trips)   // audit: the bound would have skipped this job
 
 // shared memory of the items stage (one instance per CTA)
 struct ItemShared {
@@ -170,6 +177,7 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
             const int64_t g = (int64_t)b * n + s;
             const float2 q0 = w.pos[g], q1 = w.vel[g], q2n = w.vn[g], q3 = w.acc[g];
             const uint32_t metaWord = w.meta[g];
+            const uint32_t lineWord = w.lineCand[g];   // loaded with the state (used if the ball kept its line): no extra round trip
             const int lastRail = meta_last_rail(metaWord);
             const uint32_t restMask = w.restMask[s], dynMask = w.dynMask[s];
             unsigned long long keyNow = __ldcg(key + s);   // rest / rolling offers of the strike (and whatever else is in)
@@ -182,7 +190,7 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                 // reuses the masks stored when its direction was set; the exact stages below sort out what it has passed since.
                 const bool reuse = prune && meta_kind(metaWord) == K_MOVING && R <= 24;
                 if (reuse) {
-                    const uint32_t c2 = w.lineCand[g];
+                    const uint32_t c2 = lineWord;
                     railMask = c2 & 0xffffffu;
                     pocketMask = c2 >> 24;
                 } else {
@@ -277,16 +285,16 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                 const float2* posOf = w.pos + s;
                 uint32_t candMask = 0;
                 const float corridor = diameter + 0.5f;
-                for (int o0 = 0; o0 < NB; o0 += 8) {
-                    float2 qq[8];
+                for (int o0 = 0; o0 < NB; o0 += PARTNER_BATCH) {
+                    float2 qq[PARTNER_BATCH];
                     const float2* src = posOf + (int64_t)o0 * n;
                     #pragma unroll
-                    for (int k = 0; k < 8; ++k) {   // independent loads first: one memory round trip per 8 partners
+                    for (int k = 0; k < PARTNER_BATCH; ++k) {   // independent loads first: one memory round trip per batch
                         qq[k] = (o0 + k < NB && ((restMask >> (o0 + k)) & 1u)) ? *src : make_float2(0.f, 0.f);
                         src += n;
                     }
                     #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
+                    for (int k = 0; k < PARTNER_BATCH; ++k) {
                         const float cr = dn.x * (qq[k].y - pos.y) - dn.y * (qq[k].x - pos.x);
                         if (!prune || !(fabsf(cr) > corridor)) candMask |= 1u << (o0 + k);
                     }

@@ -339,7 +339,11 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
                 Tnext[s] = newT;
                 uint32_t dynMask = w.dynMask[s], restMask = w.restMask[s];
                 const int64_t gA = (int64_t)evBall * w.n + s;
+                // the partner of a ball collision is loaded together with the event ball (one memory round trip, not two)
+                const bool pairEv = cat == CAT_STATIC_PAIR || cat == CAT_DYNAMIC_PAIR;
+                const int64_t gB = (int64_t)(pairEv ? evPartner : evBall) * w.n + s;
                 BallRec A = load_ball(w, gA);
+                BallRec B = load_ball(w, gB);
                 const v2 npos = advance_position(A.acc, A.vel, dt, A.pos);
                 const v2 nvel = advance_velocity(A.acc, A.vel, dt);
                 int cause = -1;
@@ -355,8 +359,6 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
                 } else if (evType == E_ROLLING) {          // :1810-1840
                     A.vel = nvel; A.rolling = true; A.kind = K_MOVING;
                 } else {                                   // :1842-1905 createBallCollisionNodes
-                    const int64_t gB = (int64_t)evPartner * w.n + s;
-                    BallRec B = load_ball(w, gB);
                     const v2 opos = advance_position(B.acc, B.vel, dt, B.pos);
                     const v2 ovel = advance_velocity(B.acc, B.vel, dt);
                     v2 o1, o2;
