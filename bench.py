@@ -10,7 +10,7 @@ each strike is simulated to rest, costed, the k = 1024 best valid strikes are se
 N > 1 -- merged across GPUs with one ncclAllGather of the per-GPU record blocks.
 
   value : whole-job strikes/s, inputs resident in HBM (CUDA events on the engine's stream, max over ranks)
-  e2e   : the same level through the host-buffer C-ABI calls (bcu_set_states + bcu_evaluate + bcu_level_select +
+  e2e   : the same level through the host-buffer C-ABI calls (bcu_set_states + bcu_evaluate_level (= bcu_evaluate + bcu_level_select) +
           bcu_fetch_beam): pinned host candidate arrays in; per-candidate cost / flags / potted mask / final time and the
           beam (k best strikes with their final table positions) out, wall clock
   roofline     : the simulate kernel's algorithmic FP64 work / its CUDA-event time vs. the FP64 vector issue peak
@@ -248,8 +248,7 @@ def run_b200(args, rank, local_rank, world):
 
     def e2e_step():
         eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"])
-        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True)
-        eng.level_select(BEAM)
+        res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True, select_k=BEAM)
         b = eng.fetch_beam()
         return res, b
     e2e_steps = max(1, min(args.steps, 10))

@@ -82,6 +82,9 @@ struct bcu_engine {
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
     int pruneMode = 1;                  // reach bound on ball pairs (bcu_set_prune): 0 off, 1 on, 2 audit
     uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
+    cudaStream_t copyStream = nullptr;   // bcu_evaluate_level: result copies overlap the selection kernels
+    cudaEvent_t evResults = nullptr;
+    bool beamStaged = false;         // hBeam already holds the current beam block (bcu_evaluate_level copies it ahead)
     void* hBeam = nullptr;           // pinned staging for bcu_fetch_beam
     size_t hBeamCap = 0;
     const void* beamBlock = nullptr; // the record block bcu_fetch_beam reads (local block on one rank, else the merged one)
@@ -281,6 +284,8 @@ void bcu_destroy(bcu_engine* e) {
     if (e->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->ncclComm);
     if (e->hOverflow) cudaFreeHost(e->hOverflow);
     if (e->hBeam) cudaFreeHost(e->hBeam);
+    if (e->copyStream) cudaStreamDestroy(e->copyStream);
+    if (e->evResults) cudaEventDestroy(e->evResults);
     for (int g = 0; g < PIPE_MAX_STREAMS; ++g) {
         if (e->pipeDone[g]) cudaEventDestroy(e->pipeDone[g]);
         if (e->pipeStream[g]) cudaStreamDestroy(e->pipeStream[g]);
@@ -362,11 +367,25 @@ static void fill_common(bcu_engine* e, LaunchParams& p, int64_t n, bool wantPos,
     p.out.counters = e->countersOn ? e->dCounters.p : nullptr;
 }
 
-static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out);
+static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out, cudaStream_t stream);
+static int reserve_beam_staging(bcu_engine* e, size_t bytes) {
+    if (e->hBeamCap < bytes) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->hBeam) cudaFreeHost(e->hBeam);
+        e->hBeam = nullptr; e->hBeamCap = 0;
+        CK(cudaMallocHost(&e->hBeam, bytes));
+        e->hBeamCap = bytes;
+    }
+    return BCU_OK;
+}
+extern "C" int bcu_level_select(bcu_engine* e, int32_t k);
 
 // `out` (batch path, single wave): the device->host copies of the results are queued right behind the launch, before the
 // host waits for it, so the transfer starts the moment the last kernel ends (a retry after a job-queue overflow copies again)
-static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_results* out = nullptr, bool* copied = nullptr) {
+// `selectK` > 0 (one rank): bcu_level_select is queued behind the launch as well, and the result copies move to a second
+// stream so that they overlap the selection kernels; *selected tells the caller that the beam is on its way.
+static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_results* out = nullptr, bool* copied = nullptr,
+               int selectK = 0, bool* selected = nullptr) {
     if (p.out.counters) CK(cudaMemsetAsync(p.out.counters, 0, 8 * sizeof(unsigned long long), e->stream));
     if (p.out.eventLog && trace) CK(cudaMemsetAsync(p.out.eventLog, 0xff, (size_t)p.nCand * 32 * sizeof(int4), e->stream));
     CK(cudaEventRecord(e->evStart, e->stream));
@@ -455,12 +474,36 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
                 if (useGraph) CK(cudaGraphLaunch(e->pipeGraph, e->stream));
                 e->launches += (int64_t)G * pipeline_launch_count();
                 CK(cudaEventRecord(e->evStop, e->stream));
+                bool onCopyStream = false;
                 if (out && nParts <= G) {
-                    int rc = enqueue_copy_back(e, 0, p.nCand, out);
+                    cudaStream_t cs = e->stream;
+                    if (selectK > 0 && e->nRanks == 1) {
+                        if (!e->copyStream) {
+                            CK(cudaStreamCreateWithFlags(&e->copyStream, cudaStreamNonBlocking));
+                            CK(cudaEventCreateWithFlags(&e->evResults, cudaEventDisableTiming));
+                        }
+                        CK(cudaEventRecord(e->evResults, e->stream));
+                        CK(cudaStreamWaitEvent(e->copyStream, e->evResults, 0));
+                        cs = e->copyStream;
+                        onCopyStream = true;
+                    }
+                    int rc = enqueue_copy_back(e, 0, p.nCand, out, cs);
                     if (rc) return rc;
                     if (copied) *copied = true;
+                    if (onCopyStream) {
+                        rc = bcu_level_select(e, selectK);
+                        if (rc) return rc;
+                        // the beam block follows into page-locked staging: bcu_fetch_beam only copies host memory
+                        const size_t bb = record_block_bytes(selectK, e->nBalls);
+                        rc = reserve_beam_staging(e, bb);
+                        if (rc) return rc;
+                        CK(cudaMemcpyAsync(e->hBeam, e->beamBlock, bb, cudaMemcpyDeviceToHost, e->stream));
+                        e->beamStaged = true;
+                        if (selected) *selected = true;
+                    }
                 }
                 CK(cudaStreamSynchronize(e->stream));
+                if (onCopyStream) CK(cudaStreamSynchronize(e->copyStream));
                 bool overflow = false;
                 for (int g = 0; g < G; ++g) overflow |= e->hOverflow[g] != 0;
                 if (!overflow) break;
@@ -473,34 +516,34 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
     return BCU_OK;
 }
 
-static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
+static int enqueue_copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out, cudaStream_t stream) {
     if (!out) return BCU_OK;
-    if (out->cost) CK(cudaMemcpyAsync(out->cost, e->dCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
-    if (out->flags) CK(cudaMemcpyAsync(out->flags, e->dFlags.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
-    if (out->potted) CK(cudaMemcpyAsync(out->potted, e->dPotted.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
-    if (out->final_time) CK(cudaMemcpyAsync(out->final_time, e->dFinalTime.p + offset, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (out->cost) CK(cudaMemcpyAsync(out->cost, e->dCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+    if (out->flags) CK(cudaMemcpyAsync(out->flags, e->dFlags.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    if (out->potted) CK(cudaMemcpyAsync(out->potted, e->dPotted.p + offset, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    if (out->final_time) CK(cudaMemcpyAsync(out->final_time, e->dFinalTime.p + offset, n * sizeof(float), cudaMemcpyDeviceToHost, stream));
     if (out->final_pos) {
         if (!e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "final_pos was not produced by the last launch");
         CK(cudaMemcpyAsync(out->final_pos, e->dFinalPos.p + (size_t)offset * e->nBalls * 2,
-                           (size_t)n * e->nBalls * 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+                           (size_t)n * e->nBalls * 2 * sizeof(float), cudaMemcpyDeviceToHost, stream));
     }
     if (out->event_log) {
         if (!e->last.out.eventLog) return fail(e, BCU_ERR_STATE, "event_log was not produced by the last launch");
         CK(cudaMemcpyAsync(out->event_log, e->dEventLog.p + (size_t)offset * 32, (size_t)n * 32 * sizeof(int4),
-                           cudaMemcpyDeviceToHost, e->stream));
+                           cudaMemcpyDeviceToHost, stream));
     }
     return BCU_OK;
 }
 
 static int copy_back(bcu_engine* e, int64_t offset, int64_t n, const bcu_results* out) {
-    int rc = enqueue_copy_back(e, offset, n, out);
+    int rc = enqueue_copy_back(e, offset, n, out, e->stream);
     if (rc) return rc;
     CK(cudaStreamSynchronize(e->stream));
     return BCU_OK;
 }
 
-int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float* vx, const float* vy,
-                 const uint64_t* searchCost, const uint64_t* baseCost, const bcu_results* out) {
+static int evaluate_impl(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float* vx, const float* vy,
+                         const uint64_t* searchCost, const uint64_t* baseCost, const bcu_results* out, int selectK) {
     if (!e) return BCU_ERR_INVALID;
     if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate: call bcu_set_states first");
     if (n < 0 || (n > 0 && (!stateIdx || !vx || !vy || !searchCost || !baseCost)))
@@ -530,12 +573,24 @@ int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float*
     (void)wantPos;
     p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
     p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
-    e->last = p;   // (the copies check what the launch produces)
-    bool copied = false;
-    rc = run(e, p, false, out, &copied);
+    e->last = p; e->haveLast = true; e->lastFirst = e->idBase;   // (the copies and the selection look at the launch)
+    bool copied = false, selected = false;
+    rc = run(e, p, false, out, &copied, selectK, &selected);
     if (rc) { e->haveLast = false; return rc; }
-    e->haveLast = true; e->lastFirst = e->idBase;
-    return copied ? BCU_OK : copy_back(e, 0, n, out);
+    if (!copied) { rc = copy_back(e, 0, n, out); if (rc) return rc; }
+    if (selectK > 0 && !selected) return bcu_level_select(e, selectK);
+    return BCU_OK;
+}
+
+int bcu_evaluate(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float* vx, const float* vy,
+                 const uint64_t* searchCost, const uint64_t* baseCost, const bcu_results* out) {
+    return evaluate_impl(e, n, stateIdx, vx, vy, searchCost, baseCost, out, 0);
+}
+
+int bcu_evaluate_level(bcu_engine* e, int64_t n, const int32_t* stateIdx, const float* vx, const float* vy,
+                       const uint64_t* searchCost, const uint64_t* baseCost, const bcu_results* out, int32_t k) {
+    if (k < 1 || k > 1024) return e ? fail(e, BCU_ERR_INVALID, "bcu_evaluate_level: k must be in 1..1024") : BCU_ERR_INVALID;
+    return evaluate_impl(e, n, stateIdx, vx, vy, searchCost, baseCost, out, k);
 }
 
 int bcu_evaluate_grid(bcu_engine* e, int32_t nDirs, int32_t nSpeeds, const float* dirs, const float* speeds,
@@ -736,6 +791,7 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
     }
     e->beamK = k;
     e->haveBeam = true;
+    e->beamStaged = false;
     return BCU_OK;  // asynchronous: bcu_fetch_beam / bcu_sync wait for it
 }
 
@@ -757,13 +813,11 @@ int bcu_fetch_beam(bcu_engine* e, int32_t* outCount, uint64_t* outCost, uint64_t
     // one copy of the whole record block into page-locked staging (the caller's arrays are usually pageable: five small
     // copies into them would each be staged and synchronised by the driver), then plain host copies
     const size_t bb = record_block_bytes(k, NB), need = outPos ? bb : (size_t)k * 24;
-    if (e->hBeamCap < bb) {
-        if (e->hBeam) cudaFreeHost(e->hBeam);
-        e->hBeam = nullptr; e->hBeamCap = 0;
-        CK(cudaMallocHost(&e->hBeam, bb));
-        e->hBeamCap = bb;
+    if (!e->beamStaged) {
+        int rc = reserve_beam_staging(e, bb);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(e->hBeam, e->beamBlock, need, cudaMemcpyDeviceToHost, e->stream));
     }
-    CK(cudaMemcpyAsync(e->hBeam, e->beamBlock, need, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     const char* base = (const char*)e->hBeam;
     const uint64_t* ids = (const uint64_t*)(base + (size_t)k * 8);

@@ -228,8 +228,10 @@ class Engine:
         res["flags_raw"] = res.pop("flags")   # status bits 0-7, number of events bits 8-15 (include/billiard_cuda.h)
         return res
 
-    def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False, reuse_buffers=False):
-        """reuse_buffers=True returns views of cached page-locked result buffers (overwritten by the next such call)."""
+    def evaluate(self, cand_state, vx, vy, search_cost, base_cost, final_pos=True, event_log=False, reuse_buffers=False,
+                 select_k=None):
+        """reuse_buffers=True returns views of cached page-locked result buffers (overwritten by the next such call).
+        select_k: also select the k best valid strikes (bcu_evaluate_level); fetch them with fetch_beam()."""
         vx = np.ascontiguousarray(vx, dtype=np.float32)
         vy = np.ascontiguousarray(vy, dtype=np.float32)
         n = len(vx)
@@ -237,8 +239,14 @@ class Engine:
         sc = np.ascontiguousarray(np.broadcast_to(np.asarray(search_cost, dtype=np.uint64), (n,)))
         bc = np.ascontiguousarray(np.broadcast_to(np.asarray(base_cost, dtype=np.uint64), (n,)))
         out, res = self._result_buffers(n, final_pos, event_log, reuse=reuse_buffers)
-        self._ck(self.lib.bcu_evaluate(self.h, C.c_int64(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
-                                       _p(sc, C.c_uint64), _p(bc, C.c_uint64), C.byref(res)), "bcu_evaluate")
+        if select_k:
+            self._ck(self.lib.bcu_evaluate_level(self.h, C.c_int64(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
+                                                 _p(sc, C.c_uint64), _p(bc, C.c_uint64), C.byref(res), C.c_int32(select_k)),
+                     "bcu_evaluate_level")
+            self._beam_k = select_k
+        else:
+            self._ck(self.lib.bcu_evaluate(self.h, C.c_int64(n), _p(cs, C.c_int32), _p(vx, C.c_float), _p(vy, C.c_float),
+                                           _p(sc, C.c_uint64), _p(bc, C.c_uint64), C.byref(res)), "bcu_evaluate")
         self._last_n = n
         return self._finish(out)
 

@@ -147,6 +147,11 @@ int bcu_trace_strikes(bcu_engine* e, int32_t n, const int32_t* state_idx, const 
  * block, all-gather the blocks of all ranks (one ncclAllGather; skipped for a single rank) and merge them into
  * the global top-k -- identical on every rank.  Asynchronous on the engine's stream. */
 int bcu_level_select(bcu_engine* e, int32_t k);
+/* bcu_evaluate followed by bcu_level_select(k) as ONE call: the selection is queued right behind the simulation and the
+ * per-strike result copies (out, may be NULL) run on a second stream next to it.  Returns when the results are in the
+ * caller's buffers; the beam is fetched with bcu_fetch_beam as usual.  Same arguments and errors as bcu_evaluate. */
+int bcu_evaluate_level(bcu_engine* e, int64_t n, const int32_t* state_idx, const float* vx, const float* vy,
+                       const uint64_t* search_cost, const uint64_t* base_cost, const bcu_results* out, int32_t k);
 /* Re-run the last grid launch and select again, everything resident (timing loops). */
 int bcu_level_rerun(bcu_engine* e, int32_t k);
 /* Merged beam, device -> host: *out_count valid entries (ascending); arrays sized for k (any may be NULL):

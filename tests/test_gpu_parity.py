@@ -461,3 +461,27 @@ def test_topk_dense_level_takes_the_streaming_sorter(engine):
     tc, ti = engine.topk(1024)
     kk = min(1024, len(sel))
     assert np.array_equal(ti, o2[:kk].astype(np.uint64)) and np.array_equal(tc, res["cost"][o2[:kk]])
+
+
+def test_evaluate_level_equals_evaluate_then_select(engine):
+    """bcu_evaluate_level (selection queued behind the simulation, result copies on a second stream) returns the same
+    per-strike results and the same beam as bcu_evaluate followed by bcu_level_select."""
+    from billiard_ai_b200 import workloads as W
+    pos, types = W.snooker22_open(22)
+    rng = np.random.RandomState(3)
+    n = 40000
+    ang = rng.uniform(0, 2 * np.pi, n); spd = rng.uniform(50, 5000, n)
+    vx = (spd * np.cos(ang)).astype(np.float32); vy = (spd * np.sin(ang)).astype(np.float32)
+    engine.set_states(pos, types, 1 << 1)
+    a = engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=False)
+    engine.level_select(512)
+    beam_a = engine.fetch_beam()
+    b = engine.evaluate(0, vx, vy, W.GRID_SEARCH_COST, 0, final_pos=False, select_k=512)
+    beam_b = engine.fetch_beam()
+    for key in ("cost", "flags", "potted", "n_events", "final_time"):
+        assert np.array_equal(a[key].view(np.uint32) if a[key].dtype == np.float32 else a[key],
+                              b[key].view(np.uint32) if b[key].dtype == np.float32 else b[key]), key
+    assert len(beam_a["cost"]) == len(beam_b["cost"]) > 0
+    for key in ("cost", "id", "potted"):
+        assert np.array_equal(beam_a[key], beam_b[key]), key
+    assert np.array_equal(beam_a["final_pos"].view(np.uint32), beam_b["final_pos"].view(np.uint32))

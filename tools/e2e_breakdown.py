@@ -29,8 +29,8 @@ def timed(name, fn):
 
 def step():
     timed("set_states", lambda: eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"]))
-    timed("evaluate", lambda: eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True))
-    timed("level_select", lambda: eng.level_select(BEAM))
+    timed("evaluate_level", lambda: eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True,
+                                                 select_k=BEAM))
     timed("fetch_beam", lambda: eng.fetch_beam())
 
 
