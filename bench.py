@@ -292,10 +292,10 @@ def run_b200(args, rank, local_rank, world):
     # DRAM traffic of one level's kernels from the committed ncu launch list (warm caches, single GPU, this workload)
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_v7_level_dram_inst_time.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r01_v8_level_dram_inst_time.json")) as f:
             dj = json.load(f)
         traffic = float(dj["dram_bytes_read"] + dj["dram_bytes_write"])
-        traffic_src = "profiles/r01_v7_level_dram_inst_time.json (ncu dram__bytes_read.sum + dram__bytes_write.sum over the level's launches)"
+        traffic_src = "profiles/r01_v8_level_dram_inst_time.json (ncu dram__bytes_read.sum + dram__bytes_write.sum over the level's launches)"
     except Exception:
         pass
     ach = fp64_flop / (k_ms * 1e-3) / 1e9

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """ncu launch list (--csv, metrics gpu__time_duration.sum, dram__bytes_*.sum, smsp__inst_executed.sum) -> per-level JSON.
 
-Sums the metrics per kernel name and over one level (init_kernel ... merge_records_kernel).  Two levels are reported: the
+Sums the metrics per kernel name and over one level (init_kernel ... pack_records_kernel; one rank: no record merge).  Two levels are reported: the
 one bench.py times (preceded by its L2 flush: the write-back of the flush buffer's dirty lines lands in this level's DRAM
 write count) under "after_l2_flush", and the level before it (no flush in front: the path's own traffic) at top level.  bench.py reads `dram_bytes_read + dram_bytes_write` of the file it is pointed
 at as roofline.traffic.   usage: ncu_level_json.py launches.csv "source note" > profiles/rNN_dram_per_level.json"""
@@ -19,7 +19,7 @@ def main(path, note):
         launches.setdefault(int(r[0]), dict(kernel=name))[r[12]] = v
     seq = list(launches.values())
     flush = [i for i, l in enumerate(seq) if l["kernel"] == "flush_kernel"][0]
-    ends = [i for i, l in enumerate(seq) if l["kernel"] == "merge_records_kernel"]
+    ends = [i for i, l in enumerate(seq) if l["kernel"] == "pack_records_kernel"]
     starts = [i for i, l in enumerate(seq) if l["kernel"] == "init_kernel"]
     timed = seq[flush + 1:min(e for e in ends if e > flush) + 1]
     end = max(e for e in ends if e < flush)
