@@ -765,6 +765,12 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
     if (!e->haveLast || !e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "bcu_level_select: no grid launch to select from");
     if (k < 1 || k > 1024) return fail(e, BCU_ERR_INVALID, "bcu_level_select: k must be in 1..1024");
     CK(cudaSetDevice(e->device));
+    // BCU_SELECT_TIMING=1 (diagnosis only): CUDA events between the phases, times on stderr
+    static const bool timing = getenv("BCU_SELECT_TIMING") != nullptr;
+    cudaEvent_t tv[5] = {};
+    int nt = 0;
+    auto mark = [&]() { if (timing && nt < 5) { cudaEventCreate(&tv[nt]); cudaEventRecord(tv[nt], e->stream); ++nt; } };
+    mark();
     int rc = topk_device(e, k);
     if (rc) return rc;
     const size_t bb = record_block_bytes(k, e->nBalls);
@@ -772,6 +778,7 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
     CK(launch_pack_records(e->dTopCost.p, e->dTopId.p, k, e->lastFirst, e->dPotted.p, e->dFinalTime.p, e->dFinalPos.p,
                            e->nBalls, e->dBlockLocal.p, e->stream));
     e->launches += 1;
+    mark();
     const void* gathered = e->dBlockLocal.p;
     if (e->nRanks > 1) {
         // the ONE collective of the path: per-GPU top-k records, ~ k * (24 + 8 N) bytes per rank
@@ -782,12 +789,21 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
         }
         gathered = e->dBlockAll.p;
     }
+    mark();
     if (e->nRanks > 1) {
         CK(launch_merge_records(gathered, e->nRanks, k, e->nBalls, e->dBlockMerged.p, e->stream));
         e->launches += 2;
         e->beamBlock = e->dBlockMerged.p;
     } else {
         e->beamBlock = e->dBlockLocal.p;   // one rank: the packed local block is the beam
+    }
+    mark();
+    if (timing) {
+        cudaStreamSynchronize(e->stream);
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, tv[0], tv[1]); cudaEventElapsedTime(&b, tv[1], tv[2]); cudaEventElapsedTime(&c, tv[2], tv[3]);
+        fprintf(stderr, "[bcu select] rank %d: top-k + pack %.1f us, allgather %.1f us, merge %.1f us\n", e->rank, a * 1e3f, b * 1e3f, c * 1e3f);
+        for (int i = 0; i < nt; ++i) cudaEventDestroy(tv[i]);
     }
     e->beamK = k;
     e->haveBeam = true;
