@@ -74,7 +74,15 @@ __device__ __forceinline__ void push_mask(uint32_t mask, uint32_t base, uint16_t
 //   * moving vs moving: only if dA and dV are more than 0.57 degrees apart (sin^2 >= 1e-4: q is then 4 orders of magnitude
 //     above the quantisation noise that makes the collinear case fragile) and the leading coefficient is >= 1e-5 (a = 0
 //     exactly makes the reference return "none" before solving; in between the quartic is nearly cubic).  Audits with
-//     both guards removed found no failure either (5.4e8 marked jobs); they are kept as margin.
+//     both guards removed found no failure in 5.4e8 marked jobs, but a later one (5.2e7 strikes, 16 balls) did find ONE:
+//     two rolling balls 1.08 m apart whose quantised polynomial has the roots 2.05 +- 124.7i, 2.05 +- 1.80i -- all four with
+//     the same real part, i.e. the depressed quartic's q = (b^3 - 4abc + 8a^2 d) / 8a^3 cancels to 1e-3 of its terms by
+//     accident (no collinearity: sin^2 = 0.999), S ~ 0 again, and the reference reports a "collision" at 0.108 s.  So the
+//     condition that matters is the one on q itself: the bound is used only if |b^3 - 4abc + 8a^2 d| >= 1e-2 x the sum of the
+//     magnitudes of its three terms, evaluated on the quantised binary32 coefficients the solver will see (this contains
+//     the collinear case; the two older guards stay as margin).  Measured on that polynomial with d swept through the
+//     cancellation (the reference's own solver against numpy's roots): ratio 4e-6 (the failure) garbage, 5e-5 -> roots off
+//     by 3e-3 s, 5e-4 -> 1e-4 s, 5e-3 -> 4e-7 s, 5e-2 -> 6e-9 s; the bound's own slack is 2e-3 s.
 // On top of the bound 2 ms and 2 mm of slack are left for the rounding of the solver in these regimes.  The strike's key
 // only decreases during a round, so any value read from it is a valid T.  mode 2 (audit) posts everything and marks the
 // jobs the bound would have skipped; quartic_kernel then counts the marked jobs whose result would have mattered
@@ -101,6 +109,10 @@ __device__ __forceinline__ float reach_ball(const Reach& r, float v, float a) {
 #ifndef PRUNE_MIN_SIN_SQ_V
 #define PRUNE_MIN_SIN_SQ_V 1e-4f
 #endif
+#ifndef PRUNE_MIN_QREL_V
+#define PRUNE_MIN_QREL_V 1e-2f
+#endif
+constexpr float PRUNE_MIN_QREL = PRUNE_MIN_QREL_V;   // |depressed q's numerator| / (sum of |its terms|), see above
 constexpr float PRUNE_MIN_LEADING = PRUNE_MIN_LEADING_V;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
 constexpr float PRUNE_MIN_SIN_SQ = PRUNE_MIN_SIN_SQ_V;
 constexpr uint32_t JOB_MARK = 0x80000000u;
@@ -358,6 +370,12 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                         const float aa = dot(dA, dA), vv = dot(dV, dV), cr = dA.x * dV.y - dA.y * dV.x;
                         outOfReach = 0.25f * aa >= PRUNE_MIN_LEADING && vv > 0.0f && cr * cr >= PRUNE_MIN_SIN_SQ * (aa * vv) &&
                                      !is_zero(v1) && !is_zero(w2) && dot(dP, dP) > reach * reach;
+                        if (outOfReach) {   // is the solver's S resolved?  (the depressed quartic must not be nearly biquadratic)
+                            float co[5];
+                            collision_coefficients(a1, v1, p1, a2, w2, p2, diameter, co);
+                            const float t1 = co[1] * co[1] * co[1], t2 = 4.0f * co[0] * co[1] * co[2], t3 = 8.0f * co[0] * co[0] * co[3];
+                            outOfReach = fabsf((t1 - t2) + t3) >= PRUNE_MIN_QREL * (fabsf(t1) + fabsf(t2) + fabsf(t3));
+                        }
                     }
                     // the reference tests b -> o and, on o's own turn, o -> b; the quantised coefficients of both
                     // orders are identical, so one job covers both
