@@ -9,13 +9,20 @@ candidate strikes PER GPU (weak scaling: N GPUs evaluate N x 1024 directions, sh
 each strike is simulated to rest, costed, the k = 1024 best valid strikes are selected on the device and -- for
 N > 1 -- merged across GPUs with one ncclAllGather of the per-GPU record blocks.
 
-  value : whole-job strikes/s, inputs resident in HBM (CUDA events on the engine's stream, max over ranks)
-  e2e   : the same level through the host-buffer C-ABI calls (bcu_set_states + bcu_evaluate_level (= bcu_evaluate + bcu_level_select) +
-          bcu_fetch_beam): pinned host candidate arrays in; per-candidate cost / flags / potted mask / final time and the
-          beam (k best strikes with their final table positions) out, wall clock
-  roofline     : the simulate kernel's algorithmic FP64 work / its CUDA-event time vs. the FP64 vector issue peak
-                 measured in the same run (un-fused DADD+DMUL: FMA contraction is forbidden on this path)
-  cpu_baseline : the reference's own CPU code (oracle/_ref/libref_oracle.so) on a bounded sample, all host threads
+  value : whole-job strikes/s, inputs resident in HBM (CUDA events on the engine's stream, max over ranks), with the
+          reach bound ON (bcu_set_prune 1: audited, not proven -- DESIGN.md section 4)
+  value_exact : the same with the reach bound OFF (the C ABI's default: every test and every quartic of the reference)
+  e2e / e2e_exact : the same level through the host-buffer C-ABI calls (bcu_set_states + bcu_evaluate_level (= bcu_evaluate
+          + bcu_level_select) + bcu_fetch_beam): pinned host candidate arrays in; per-candidate cost / flags / potted mask /
+          final time and the beam (k best strikes with their final table positions) out, wall clock
+  parity : every strike of the timed workload (all N x 65 536) against the reference's own code on the host cores, once per
+          run, untimed: mismatches, best strike, and -- N > 1 -- the merged beam against one GPU evaluating the whole grid
+  roofline     : the pipeline's FP64 work / its CUDA-event time vs. the FP64 vector issue peak measured in the same run
+                 (un-fused DADD+DMUL: FMA contraction is forbidden on this path); three fractions: algorithmic (the
+                 reference's quartic count), executed (quartics actually solved), issue-slot utilisation
+  cpu_baseline : the reference's own CPU code (oracle/_ref/libref_oracle.so) on the whole grid of one GPU, all host threads
+  stats, extra : a longer timed region (>= 200 steps: mean / median / p95) and secondary workloads (16-ball level, config 5
+                 slice, multi-break searches), each with both prune modes
 
 --impl reference times the reference CPU implementation only (rank 0).
 """
@@ -115,48 +122,38 @@ def sharded_grid(world):
     return np.ascontiguousarray(dirs[order]), speeds
 
 
-def reference_sample(world, n_sample):
-    from billiard_ai_b200 import workloads as W
-    dirs, speeds = sharded_grid(world)
-    vx, vy = W.grid_velocities(dirs, speeds)
-    total = len(vx)
-    idx = (np.arange(n_sample, dtype=np.int64) * 2654435761) % total  # fixed pseudo-random sample of the grid
-    return vx[idx], vy[idx]
-
-
-def time_reference(oracle, world, n_sample, threads):
+def reference_pass(oracle, world, threads, shard=None):
+    """One pass of the reference's CPU code over the candidates of the bench workload -- the same grid, the same ids --
+    either all N x 65 536 of them (shard None: the parity check) or one GPU's shard of 65 536 (the timed CPU baseline).
+    -> (results, seconds)"""
     from billiard_ai_b200 import workloads as W
     pos, types = W.snooker22_open()
-    vx, vy = reference_sample(world, n_sample)
+    dirs, speeds = sharded_grid(world)
+    vx, vy = W.grid_velocities(dirs, speeds)
+    if shard is not None:
+        lo, hi = W.shard_range(len(vx), shard, world)
+        vx, vy = vx[lo:hi], vy[lo:hi]
     t0 = time.perf_counter()
-    out = oracle.evaluate(pos[None], types[None], 1 << W.TYPE_CODE["RED"], 0, vx, vy, W.GRID_SEARCH_COST, 0,
-                          threads=threads)
-    dt = time.perf_counter() - t0
-    return n_sample / dt, int(out["n_events"].sum()) / dt, dt
-
-
-def calibrate_sample(oracle, world, threads, target_s):
-    n = 64 * threads
-    for _ in range(2):  # the first probe is dominated by thread start-up
-        rate, _, _ = time_reference(oracle, world, n, threads)
-        n = (int(max(256, min(1 << 20, rate * target_s))) + 63) // 64 * 64
-    return n
+    out = oracle.evaluate(pos[None], types[None], 1 << W.TYPE_CODE["RED"], 0, vx, vy, W.GRID_SEARCH_COST, 0, threads=threads)
+    return out, time.perf_counter() - t0
 
 
 def run_reference(args, rank, world):
+    """The reference arm: the reference's own CPU implementation of the path on the box's host cores.  A step is one pass
+    over ONE GPU's shard of the workload (all 65 536 candidates of shard 0: at N = 1 that is the whole workload)."""
     if rank != 0:
         return
     oracle, kind = load_reference()
     threads = os.cpu_count() or 1
-    n_sample = calibrate_sample(oracle, world, threads, target_s=4.0)
-    for _ in range(min(args.warmup, 1)):
-        time_reference(oracle, world, max(256, n_sample // 8), threads)
-    tot_t, tot_n, tot_ev = 0.0, 0, 0.0
+    for _ in range(min(args.warmup, 2)):
+        reference_pass(oracle, world, threads, shard=0)
+    tot_t, tot_n, tot_ev = 0.0, 0, 0
     for _ in range(args.steps):
-        r, ev, dt = time_reference(oracle, world, n_sample, threads)
-        tot_t += dt; tot_n += n_sample; tot_ev += ev * dt
+        out, dt = reference_pass(oracle, world, threads, shard=0)
+        tot_t += dt; tot_n += len(out["cost"]); tot_ev += int(out["n_events"].sum())
     value = tot_n / tot_t
-    sample = f"{n_sample} of {N_DIRS * N_SPEEDS * world} grid candidates per step (fixed multiplicative-hash sample)"
+    sample = (f"every step = all {N_DIRS * N_SPEEDS} candidates of shard 0 of {world} (the same grid and ids the GPU arm "
+              f"evaluates; {N_DIRS * N_SPEEDS * world} in the whole job)")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
@@ -167,6 +164,43 @@ def run_reference(args, rank, world):
 
 
 # ---- B200 arm -------------------------------------------------------------------------------------------------
+def measured_op_counts():
+    """Per-kernel FP instruction counts of one level of this workload from the committed ncu pass
+    (profiles/r02_level_fp_ops.json, tools/ncu_fp_ops.py): replaces SURVEY.md's working figure of 1000 FP64 FLOP per
+    quartic by what the quartic kernel executes.  None when the file is absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_level_fp_ops.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def compare_with_reference(got, want, tie):
+    """-> (tie-free strikes compared, mismatching strikes): integers equal, floats bit-equal."""
+    n = len(want["cost"])
+    clean = tie["min_gap"] >= 1e-9 if tie is not None and tie.get("min_gap") is not None else np.ones(n, bool)
+    bad = np.zeros(n, bool)
+    for key in ("cost", "flags", "n_events", "potted"):
+        bad |= got[key] != want[key]
+    bad |= got["final_time"].view(np.uint32) != want["final_time"].view(np.uint32)
+    bad |= (got["final_pos"].view(np.uint32) != want["final_pos"].view(np.uint32)).reshape(n, -1).any(axis=1)
+    return int(clean.sum()), int((bad & clean).sum()), clean
+
+
+def timed_levels(eng, steps, barrier):
+    """`steps` levels, L2 flushed before each, CUDA events on the engine's stream -> per-step ms, per-step kernel ms."""
+    step_ms, kernel_ms = [], []
+    barrier()
+    for _ in range(steps):
+        eng.flush_l2()
+        eng.timer_begin()
+        eng.level_rerun(BEAM)
+        step_ms.append(eng.timer_end())
+        kernel_ms.append(eng.last_kernel_ms())
+    barrier()
+    return step_ms, kernel_ms
+
+
 def run_b200(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -185,12 +219,11 @@ def run_b200(args, rank, local_rank, world):
         eng.comm_init(world, rank, box[0])
 
     pos, types = W.snooker22_open()
+    red = 1 << W.TYPE_CODE["RED"]
     dirs, speeds = sharded_grid(world)
     total = len(dirs) * len(speeds)
     lo, hi = W.shard_range(total, rank, world)
     mine = hi - lo
-    eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"])
-    eng.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=lo, count=mine)   # uploads + first launch
 
     def barrier():
         if world > 1:
@@ -198,38 +231,41 @@ def run_b200(args, rank, local_rank, world):
         torch.cuda.synchronize()
         eng.sync()
 
-    # ---- warm-up ------------------------------------------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        eng.level_rerun(BEAM)
-    eng.sync()
+    def allmax(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    # ---- timed: value (resident inputs) ----------------------------------------------------------------------
+    def resident_launch(prune):
+        eng.set_prune(prune)
+        eng.set_states(pos, types, red)
+        eng.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=lo, count=mine)   # uploads + first launch
+        for _ in range(max(args.warmup, 3)):
+            eng.level_rerun(BEAM)
+        eng.sync()
+
+    # ---- timed: value (resident inputs, reach bound on) ------------------------------------------------------------
+    resident_launch(1)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
     launches0 = eng.launch_count()
-    barrier()
     wall0 = time.perf_counter()
-    step_ms, kernel_ms = [], []
-    for _ in range(args.steps):
-        eng.flush_l2()
-        eng.timer_begin()
-        eng.level_rerun(BEAM)
-        step_ms.append(eng.timer_end())
-        kernel_ms.append(eng.last_kernel_ms())
-    barrier()
+    step_ms, kernel_ms = timed_levels(eng, args.steps, barrier)
     wall = time.perf_counter() - wall0
     launches = eng.launch_count() - launches0
+    t_ms = allmax(float(np.sum(step_ms)))
+    # a longer region on the same launch: spread of the step time (the K-step region above is the contract's number)
+    long_steps = max(200, args.steps)
+    long_ms, _ = timed_levels(eng, long_steps, barrier)
     clocks = sampler.stop() if rank == 0 else None
-    t_ms = float(np.sum(step_ms))
-    if world > 1:
-        t = torch.tensor([t_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_ms = float(t.item())
+    long_sum = allmax(float(np.sum(long_ms)))
     beam = eng.fetch_beam()
 
-    # ---- work counters (untimed extra launch) -> events/s and the roofline's algorithmic work ------------------
+    # ---- work counters (untimed extra launches) -> events/s and the roofline's work ---------------------------------
     eng.enable_counters(True)
     eng.rerun()
     cnt = eng.counters()
@@ -246,7 +282,15 @@ def run_b200(args, rank, local_rank, world):
         dist.all_reduce(cvec)
     ev_total = float(cvec[0].item())
 
-    # ---- e2e: host buffers through the C ABI -----------------------------------------------------------------------
+    # ---- timed: value_exact (reach bound off: the C ABI's default) ----------------------------------------------------
+    resident_launch(0)
+    exact_ms, exact_kernel_ms = timed_levels(eng, args.steps, barrier)
+    t_exact_ms = allmax(float(np.sum(exact_ms)))
+    beam_exact = eng.fetch_beam()
+    assert np.array_equal(beam_exact["cost"], beam["cost"]) and np.array_equal(beam_exact["id"], beam["id"]), \
+        "reach bound on / off select different beams"
+
+    # ---- e2e: host buffers through the C ABI ---------------------------------------------------------------------------
     vx_all, vy_all = W.grid_velocities(dirs, speeds)
 
     def pinned(a):
@@ -258,37 +302,97 @@ def run_b200(args, rank, local_rank, world):
     eng.set_id_base(lo)
 
     def e2e_step():
-        eng.set_states(pos, types, 1 << W.TYPE_CODE["RED"])
+        eng.set_states(pos, types, red)
         res = eng.evaluate(hst, hvx, hvy, hsc, hbc, final_pos=False, event_log=False, reuse_buffers=True, select_k=BEAM)
         b = eng.fetch_beam()
         return res, b
     e2e_steps = max(1, min(args.steps, 10))
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        res, b2 = e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    assert np.array_equal(b2["cost"], beam["cost"]) and np.array_equal(b2["id"], beam["id"]), "e2e beam != resident beam"
+
+    def e2e_run(prune):
+        eng.set_prune(prune)
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            res, b2 = e2e_step()
+        barrier()
+        secs = allmax(time.perf_counter() - t0)
+        assert np.array_equal(b2["cost"], beam["cost"]) and np.array_equal(b2["id"], beam["id"]), "e2e beam != resident beam"
+        return secs
+    e2e_s = e2e_run(1)
+    e2e_exact_s = e2e_run(0)
     nb = len(types)
     h2d = mine * (4 + 4 + 4 + 8 + 8) + nb * (8 + 4) + 4
     d2h = mine * (8 + 4 + 4 + 4) + BEAM * (24 + nb * 8)   # per-strike cost / flags / potted / time + the beam records
 
     if rank != 0:
+        barrier()           # rank 0 checks parity on its own GPU meanwhile (no collective in there)
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the simulate stage: the strike pipeline's kernels (items / quartic / apply per event round), timed
-    #      together with CUDA events on the engine's stream; its FP64 work is the quartic kernel's ------------------------
+    # ---- parity: every strike of the timed workload against the reference's own code, untimed ----------------------------
+    #      (rank 0 evaluates the WHOLE N x 65 536 grid on its own GPU, so at N > 1 the merged beam of the N ranks is checked
+    #      against a single-GPU evaluation as well as against the reference)
+    parity, cpu = None, None
+    if not args.no_cpu_baseline:
+        oracle, kind = load_reference()
+        import oracle_lib
+        threads = os.cpu_count() or 1
+        want, _ = reference_pass(oracle, world, threads)
+        tie = None
+        if os.path.exists(oracle_lib.PORT_SO):   # near-tie information (the port is bit-identical to the reference build)
+            tie, _ = reference_pass(oracle_lib.PortOracle(), world, threads)
+        parity = {"reference": kind, "compared": 0, "mismatches": 0}
+        for prune in (1, 0):
+            eng.set_prune(prune)
+            eng.set_states(pos, types, red)
+            eng.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST, first=0, count=total)
+            got = eng.fetch()
+            compared, bad, clean = compare_with_reference(got, want, tie)
+            parity["compared"] += compared if prune == 1 else 0
+            parity["mismatches"] += bad
+            parity[f"mismatches_prune{prune}"] = bad
+        ids = np.nonzero((want["flags"] & 2) != 0)[0]
+        order = ids[np.lexsort((ids, want["cost"][ids]))][:BEAM]
+        tc, ti = eng.topk(BEAM)     # the whole grid on this one GPU, no collective
+        parity["near_ties"] = int((~clean).sum())
+        parity["best_strike_equal"] = bool(len(order) and len(beam["id"]) and int(beam["id"][0]) == int(order[0])
+                                           and int(beam["cost"][0]) == int(want["cost"][order[0]]))
+        parity["beam_equals_reference_topk"] = bool(np.array_equal(beam["id"], order.astype(np.uint64))
+                                                    and np.array_equal(beam["cost"], want["cost"][order]))
+        parity["merged_beam_equals_single_gpu"] = bool(np.array_equal(beam["id"], ti) and np.array_equal(beam["cost"], tc))
+        gpos, gpot, _ = eng.gather(beam["id"])
+        parity["beam_end_states_equal"] = bool(np.array_equal(gpos.view(np.uint32), beam["final_pos"].view(np.uint32))
+                                               and np.array_equal(gpot, beam["potted"])
+                                               and np.array_equal(gpos.view(np.uint32),
+                                                                  want["final_pos"][order].view(np.uint32)))
+        # ---- CPU baseline: the reference's own code over one GPU's shard (all 65 536 candidates), all host threads ----
+        reference_pass(oracle, world, threads, shard=0)
+        reps, tsum, evs, nst = 3, 0.0, 0, 0
+        for _ in range(reps):
+            out, dt = reference_pass(oracle, world, threads, shard=0)
+            tsum += dt; evs += int(out["n_events"].sum()); nst += len(out["cost"])
+        cpu = {"value": nst / tsum, "unit": UNIT, "cores": threads, "kind": kind, "events_per_sec": evs / tsum,
+               "sample": f"{reps} passes over all {nst // reps} candidates of shard 0 (same grid and ids as the GPU arm), {tsum:.1f} s"}
+    eng.set_prune(1)
+
+    # ---- secondary workloads (device-timed, resident inputs, both prune modes) -----------------------------------------
+    extra = None
+    if not args.no_extra:
+        extra = secondary_workloads(eng, W, args)
+    barrier()
+
+    # ---- roofline of the strike pipeline (init + 31 x {items, quartic, apply} + finish), timed together with CUDA events
+    #      on the engine's stream; its FP64 work is the quartic kernel's ---------------------------------------------------
     k_ms = float(np.mean(kernel_ms))
     per_rank = cvec.cpu().numpy() / world
-    fp64_flop = per_rank[2] * W_QUARTIC_FP64
+    ops = measured_op_counts()
+    w_quartic = float(ops["fp64_flop_per_quartic"]) if ops else W_QUARTIC_FP64
+    w_src = ("profiles/r02_level_fp_ops.json: FP64 thread-instructions of quartic_kernel (DADD + DMUL + 2 x DFMA) / quartics solved, ncu"
+             if ops else "SURVEY.md 8d working figure (no ncu count committed)")
+    fp64_alg = per_rank[2] * w_quartic          # the reference's quartic count
+    fp64_exec = per_rank[5] * w_quartic         # quartics this build solves
     fp32_flop = (per_rank[1] * W_PAIR + per_rank[3] * W_RAIL + per_rank[4] * W_POCKET + per_rank[0] * nb * W_ADVANCE)
     peak_dp = eng.issue_rate(0)
     peak_dfma = eng.issue_rate(1)
@@ -300,54 +404,112 @@ def run_b200(args, rank, local_rank, world):
             hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
         hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
-    # DRAM traffic of one level's kernels from the committed ncu launch list (warm caches, single GPU, this workload)
-    traffic, traffic_src = None, None
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_v8_level_dram_inst_time.json")) as f:
-            dj = json.load(f)
-        traffic = float(dj["dram_bytes_read"] + dj["dram_bytes_write"])
-        traffic_src = "profiles/r01_v8_level_dram_inst_time.json (ncu dram__bytes_read.sum + dram__bytes_write.sum over the level's launches)"
-    except Exception:
-        pass
-    ach = fp64_flop / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "fp64_vector", "kernel": "strike pipeline (init + 31 x {items, quartic, apply} + finish; FP64 work = quartic_kernel)", "achieved": ach, "peak": peak_dp,
-                "unit": "GFLOP/s", "frac": ach / peak_dp, "traffic": traffic, "traffic_source": traffic_src,
+    # DRAM traffic and warp instructions of one level's kernels from the committed ncu launch list (this workload, one GPU)
+    traffic, traffic_src, warp_inst = None, None, None
+    for name in ("r02_level_dram_inst_time.json", "r01_v8_level_dram_inst_time.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                dj = json.load(f)
+            traffic = float(dj["dram_bytes_read"] + dj["dram_bytes_write"])
+            warp_inst = float(dj.get("warp_instructions", 0)) or None
+            traffic_src = f"profiles/{name} (ncu dram__bytes_read.sum + dram__bytes_write.sum over the level's launches)"
+            break
+        except Exception:
+            continue
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    issue_frac = (warp_inst / (k_ms * 1e-3) / (148 * 4 * sm_mhz * 1e6)) if warp_inst else None
+    ach_alg = fp64_alg / (k_ms * 1e-3) / 1e9
+    ach_exec = fp64_exec / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "fp64_vector", "kernel": "strike pipeline (init + 31 x {items, quartic, apply} + finish; FP64 work = quartic_kernel)",
+                "achieved": ach_exec, "peak": peak_dp, "unit": "GFLOP/s", "frac": ach_exec / peak_dp,
+                "frac_executed": ach_exec / peak_dp,
+                "frac_algorithmic": ach_alg / peak_dp,
+                "frac_issue_slots": issue_frac,
+                "fractions_note": "executed = quartics this build solves x measured FP64 FLOP per quartic; algorithmic = the "
+                                  "reference's quartic count x the same (the reach bound skips the difference); issue slots = "
+                                  "warp instructions of a level / (kernel ms x 592 issue slots per clock x SM clock)",
+                "fp64_flop_per_quartic": w_quartic, "fp64_flop_per_quartic_source": w_src,
+                "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "measured in this run: un-fused DADD+DMUL issue rate (FMA contraction is forbidden on "
                                "this path); DFMA rate x2 listed for context",
                 "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (t_ms / args.steps),
-                "alg_fp64_flop_per_launch": fp64_flop, "alg_fp32_flop_per_launch": fp32_flop,
+                "alg_fp64_flop_per_launch": fp64_alg, "exec_fp64_flop_per_launch": fp64_exec,
+                "alg_fp32_flop_per_launch": fp32_flop, "warp_instructions_per_launch": warp_inst,
                 "fp32": {"achieved": fp32_flop / (k_ms * 1e-3) / 1e9, "peak": peak_sp, "unit": "GFLOP/s"},
                 "dfma_peak_gflops": 2 * peak_dfma, "ffma_peak_gflops": 2 * peak_ffma,
                 "hbm": {"achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "peak_source": hbm_src},
                 "work_per_strike": {"events": per_rank[0] / mine, "quartics": per_rank[2] / mine,
                                     "quartics_solved": per_rank[5] / mine},
-                "work_note": "algorithmic work = what the reference computes for these strikes (SURVEY.md 8d); the reach "
-                             "bound (DESIGN.md 4) leaves quartics_solved of the quartics per strike to the FP64 pipe"}
-
-    # ---- CPU baseline (reference's own code, bounded sample) ----------------------------------------------------
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        oracle, kind = load_reference()
-        threads = os.cpu_count() or 1
-        n_sample = calibrate_sample(oracle, 1, threads, target_s=8.0)
-        rate, ev_rate, dt = time_reference(oracle, 1, n_sample, threads)
-        cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": kind, "events_per_sec": ev_rate,
-               "sample": f"{n_sample} of {total} grid candidates (fixed multiplicative-hash sample), {dt:.1f} s wall"}
+                "exact": {"kernel_ms": float(np.mean(exact_kernel_ms)),
+                          "achieved": fp64_alg / (float(np.mean(exact_kernel_ms)) * 1e-3) / 1e9,
+                          "frac": fp64_alg / (float(np.mean(exact_kernel_ms)) * 1e-3) / 1e9 / peak_dp,
+                          "note": "reach bound off: executed == algorithmic"}}
 
     value = total * args.steps / (t_ms * 1e-3)
+    lm = np.array(long_ms)
+    cfg = workload_desc(world)
+    cfg["prune"] = ("value / e2e: reach bound ON (bcu_set_prune 1, opt-in; audited, not proven: DESIGN.md 4); value_exact / "
+                    "e2e_exact: OFF (the C ABI's default)")
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": t_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
-            "config": workload_desc(world), "events_per_sec": ev_total * args.steps / (t_ms * 1e-3),
+            "config": cfg, "events_per_sec": ev_total * args.steps / (t_ms * 1e-3),
+            "value_exact": total * args.steps / (t_exact_ms * 1e-3), "ms_per_step_exact": t_exact_ms / args.steps,
             "wall_s_timed_region": wall, "clocks": clocks,
+            "stats": {"steps": long_steps, "value": total * long_steps / (long_sum * 1e-3), "ms_mean": float(lm.mean()),
+                      "ms_median": float(np.median(lm)), "ms_p95": float(np.percentile(lm, 95)), "ms_min": float(lm.min()),
+                      "ms_max": float(lm.max()), "note": "rank 0's per-step device times; value = max-over-ranks sum"},
             "e2e": {"value": total * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
-            "best_strike": {"cost": int(beam["cost"][0]), "id": int(beam["id"][0])} if len(beam["cost"]) else None}
+            "e2e_exact": {"value": total * e2e_steps / e2e_exact_s, "unit": UNIT, "steps": e2e_steps},
+            "gpu_launches": launches, "parity": parity, "roofline": roofline, "cpu_baseline": cpu,
+            "best_strike": {"cost": int(beam["cost"][0]), "id": int(beam["id"][0])} if len(beam["cost"]) else None,
+            "extra": extra}
     emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def secondary_workloads(eng, W, args):
+    """Device-timed secondary measurements on rank 0's GPU (resident inputs, L2 flushed before each timed launch, CUDA
+    events on the engine's stream; both prune modes): the 16-ball level the north_star target is quoted on and a slice of
+    config 5 (random 16-ball tables x 4 096 strikes)."""
+    out = {}
+    red = 1 << W.TYPE_CODE["RED"]
+
+    def timed(n_strikes, reps):
+        res = {}
+        for prune, key in ((1, "strikes_per_sec"), (0, "strikes_per_sec_exact")):
+            eng.set_prune(prune)
+            eng.rerun(); eng.rerun()
+            ms = []
+            for _ in range(reps):
+                eng.flush_l2()
+                eng.timer_begin()
+                eng.rerun()
+                ms.append(eng.timer_end())
+            res[key] = n_strikes / (float(np.mean(ms)) * 1e-3)
+            res["ms" if prune else "ms_exact"] = float(np.mean(ms))
+        eng.enable_counters(True)
+        eng.rerun()
+        res["events_per_sec_exact"] = eng.counters()["events"] / (res["ms_exact"] * 1e-3)
+        eng.enable_counters(False)
+        return res
+    pos, types = W.random_layout(16, 16)
+    dirs, speeds = W.grid(N_DIRS, N_SPEEDS)
+    eng.set_states(pos, types, red)
+    eng.evaluate_grid(dirs, speeds, W.GRID_SEARCH_COST)
+    out["level_16_balls"] = dict(workload="16-ball layout (seed 16), 1024 x 64 = 65536 strikes, one level", **timed(65536, 10))
+    nt = 1000
+    tp, tt = W.random_tables(nt, 16, seed0=1000)
+    d5, s5 = W.grid(64, 64)
+    eng.set_states(tp, tt, red)
+    eng.evaluate_grid(d5, s5, W.GRID_SEARCH_COST)
+    out["config5_slice"] = dict(workload=f"config 5: tables 1000..{1000 + nt - 1} (16 balls) x 4096 strikes = {nt * 4096} strikes, one launch",
+                                **timed(nt * 4096, 3))
+    eng.set_prune(1)
+    return out
 
 
 def emit(line):
@@ -368,7 +530,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the reference passes (parity + cpu_baseline)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

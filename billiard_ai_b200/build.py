@@ -66,6 +66,49 @@ def build(force=False, verbose=False, extra=()):
     return OUT
 
 
+# Guard variants of the reach bound (csrc/bcu_items.cuh): each threshold x 10 and / 10, and builds with one guard removed.
+# tests/test_gpu_prune_regressions.py runs the committed regression vectors through them: the weakened builds must FAIL on the
+# vectors (so the vectors demonstrably exercise the guards), the default and the x / 10 builds must pass (the margin).
+VARIANT_DIR = os.path.join(HERE, "_variants")
+GUARD_VARIANTS = {
+    "qrel0": ["-DPRUNE_MIN_QREL_V=0.0f"],
+    "restall": ["-DPRUNE_REST_PASS_ONLY_V=0"],
+    "qrel_x10": ["-DPRUNE_MIN_QREL_V=1e-1f"], "qrel_d10": ["-DPRUNE_MIN_QREL_V=1e-3f"],
+    "sin_x10": ["-DPRUNE_MIN_SIN_SQ_V=1e-3f"], "sin_d10": ["-DPRUNE_MIN_SIN_SQ_V=1e-5f"],
+    "lead_x10": ["-DPRUNE_MIN_LEADING_V=1e-4f"], "lead_d10": ["-DPRUNE_MIN_LEADING_V=1e-6f"],
+}
+
+
+def variant_path(name):
+    return os.path.join(VARIANT_DIR, f"lib_{name}.so")
+
+
+def build_variants(names=None, force=False):
+    """Only bcu_pipeline.cu depends on the guard macros: one object per variant (in parallel), linked with the default
+    build's other objects.  -> {name: path}"""
+    build(force=False)
+    os.makedirs(VARIANT_DIR, exist_ok=True)
+    names = list(GUARD_VARIANTS) if names is None else list(names)
+    flags = [f for f in NVCC_FLAGS if f not in ("-shared", "-ldl")]
+    src = os.path.join(CSRC, "bcu_pipeline.cu")
+    newest = max(os.path.getmtime(d) for d in _deps())
+    procs = []
+    for name in names:
+        obj = os.path.join(OBJDIR, f"variant_{name}.o")
+        if not force and os.path.exists(variant_path(name)) and os.path.getmtime(variant_path(name)) > newest:
+            continue
+        cmd = [nvcc_path()] + flags + GUARD_VARIANTS[name] + ["-c", src, "-o", obj]
+        procs.append((name, obj, cmd, subprocess.Popen(cmd, stderr=subprocess.DEVNULL)))
+    for name, obj, cmd, pr in procs:
+        if pr.wait() != 0:
+            raise subprocess.CalledProcessError(pr.returncode, cmd)
+        others = [os.path.join(OBJDIR, os.path.splitext(s)[0] + ".o") for s in SOURCES if s != "bcu_pipeline.cu"]
+        subprocess.check_call([nvcc_path(), "-shared", "-o", variant_path(name), obj] + others + ["-ldl"])
+    return {n: variant_path(n) for n in names}
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print(OUT)
+    if "--variants" in sys.argv:
+        print(build_variants(force="--force" in sys.argv))

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -80,7 +81,17 @@ struct bcu_engine {
     DevBuf<unsigned char> dPipeWs;   // workspace of the batch pipeline (bcu_pipeline.cu)
     int sms = 148;
     int jobsPerStrike = PIPE_JOBS_PER_STRIKE;
-    int pruneMode = 1;                  // reach bound on ball pairs (bcu_set_prune): 0 off, 1 on, 2 audit
+    int pruneMode = 0;                  // reach bound on ball pairs (bcu_set_prune): 0 off (default: every quartic the
+                                        // reference solves is solved), 1 on (opt-in: audited, not proven), 2 audit
+    PipeLaunchCfg pipeCfg;              // occupancy-sized grids, PDL mode, round timing: per engine, nothing process-wide
+    bool selectTiming = false;          // BCU_SELECT_TIMING (diagnosis)
+    int8_t* hTypeStage = nullptr;       // pinned staging of bcu_set_states' type codes (no per-call synchronisation)
+    size_t hTypeStageCap = 0;
+    cudaEvent_t evStage = nullptr;      // the last copy out of hTypeStage
+    // single-strike trace (bcu_simulate_trace): its own one-state table, so a trace never clobbers the uploaded beam
+    DevBuf<float> dTrPos;
+    DevBuf<int8_t> dTrType;
+    DevBuf<uint32_t> dTrExpected;
     uint32_t* hOverflow = nullptr;   // pinned, one word per pipeline stream
     cudaStream_t copyStream = nullptr;   // bcu_evaluate_level: result copies overlap the selection kernels
     cudaEvent_t evResults = nullptr;
@@ -134,8 +145,12 @@ struct NcclApi {
     int (*CommDestroy)(void*) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
+// The one piece of process-wide state: the function table of the dlopen'ed NCCL library (a shared object is loaded once per
+// process whatever we do).  Filled once under a lock; read-only afterwards.
 NcclApi g_nccl;
+std::mutex g_ncclLock;
 bool load_nccl(const char* path, std::string* err) {
+    std::lock_guard<std::mutex> guard(g_ncclLock);
     if (g_nccl.lib) return true;
     const char* cands[] = {path, getenv("BCU_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
     void* h = nullptr;
@@ -251,6 +266,9 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     }
     cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
     if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
+    e->pipeCfg.roundTiming = getenv("BCU_ROUND_TIMING") != nullptr;
+    if (const char* pv = getenv("BCU_PDL")) e->pipeCfg.pdlMode = atoi(pv);
+    e->selectTiming = getenv("BCU_SELECT_TIMING") != nullptr;
     if (const char* jv = getenv("BCU_JOBS_PER_STRIKE")) {   // initial quartic-queue capacity (tests force the overflow path)
         const int v = atoi(jv);
         e->jobsPerStrike = v < 1 ? 1 : v > 1024 ? 1024 : v;
@@ -278,6 +296,9 @@ void bcu_destroy(bcu_engine* e) {
     e->dCost.release(); e->dFlags.release(); e->dPotted.release(); e->dFinalTime.release(); e->dFinalPos.release();
     e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dPipeWs.release();
     e->dTable.release(); e->dRules.release();
+    e->dTrPos.release(); e->dTrType.release(); e->dTrExpected.release();
+    if (e->hTypeStage) cudaFreeHost(e->hTypeStage);
+    if (e->evStage) cudaEventDestroy(e->evStage);
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
     e->dGatherIds.release(); e->dGatherPos.release(); e->dGatherTime.release(); e->dGatherPotted.release();
     e->dBlockLocal.release(); e->dBlockAll.release(); e->dBlockMerged.release(); e->dFlush.release(); e->dSink.release();
@@ -322,25 +343,33 @@ int bcu_set_states(bcu_engine* e, int32_t nStates, int32_t nBalls, const float* 
         return fail(e, BCU_ERR_INVALID, "bcu_set_states: bad arguments");
     CK(cudaSetDevice(e->device));
     const size_t nb = (size_t)nStates * nBalls;
-    std::vector<int8_t> t8(nb);
-    int cue = 0;
+    // The 8-bit type codes are built in page-locked staging owned by the engine, so the call does not have to wait for its
+    // copies (copies from the caller's pageable arrays are staged by the runtime before cudaMemcpyAsync returns).
+    if (!e->evStage) CK(cudaEventCreateWithFlags(&e->evStage, cudaEventDisableTiming));
+    else CK(cudaEventSynchronize(e->evStage));   // the previous upload has left the staging (normally long ago)
+    if (e->hTypeStageCap < nb) {
+        if (e->hTypeStage) cudaFreeHost(e->hTypeStage);
+        e->hTypeStage = nullptr; e->hTypeStageCap = 0;
+        CK(cudaMallocHost(&e->hTypeStage, nb + nb / 4 + 64));
+        e->hTypeStageCap = nb + nb / 4 + 64;
+    }
+    int8_t* t8 = e->hTypeStage;
     for (size_t i = 0; i < nb; ++i) {
         if (types[i] >= e->rules.nTypes) return fail(e, BCU_ERR_INVALID, "bcu_set_states: type code out of range");
         t8[i] = (int8_t)(types[i] < 0 ? -1 : types[i]);
-        cue += types[i] == e->rules.cueType;
     }
     CK(e->dStatePos.reserve(nb * 2));
     CK(e->dStateType.reserve(nb));
     CK(e->dExpected.reserve(nStates));
     CK(cudaMemcpyAsync(e->dStatePos.p, pos, nb * 2 * sizeof(float), cudaMemcpyHostToDevice, e->stream));
-    CK(cudaMemcpyAsync(e->dStateType.p, t8.data(), nb, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dStateType.p, t8, nb, cudaMemcpyHostToDevice, e->stream));
+    CK(cudaEventRecord(e->evStage, e->stream));
     CK(cudaMemcpyAsync(e->dExpected.p, expectedMask, nStates * sizeof(uint32_t), cudaMemcpyHostToDevice, e->stream));
     e->hasStateBase = baseCost != nullptr;
     if (baseCost) {
         CK(e->dStateBase.reserve(nStates));
         CK(cudaMemcpyAsync(e->dStateBase.p, baseCost, nStates * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
     }
-    CK(cudaStreamSynchronize(e->stream));  // t8 is a temporary
     e->nStates = nStates;
     e->nBalls = nBalls;
     e->haveLast = false;
@@ -348,6 +377,7 @@ int bcu_set_states(bcu_engine* e, int32_t nStates, int32_t nBalls, const float* 
 }
 
 static int reserve_results(bcu_engine* e, int64_t n, bool wantPos, bool wantLog) {
+    if (n < 1) n = 1;   // an empty shard still gets valid (unused) result pointers
     CK(e->dCost.reserve(n)); CK(e->dFlags.reserve(n)); CK(e->dPotted.reserve(n)); CK(e->dFinalTime.reserve(n));
     if (wantPos) CK(e->dFinalPos.reserve((size_t)n * e->nBalls * 2));
     if (wantLog) CK(e->dEventLog.reserve((size_t)n * 32));
@@ -399,6 +429,10 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
         // sequence is captured once into a CUDA graph (kernel parameters live in device memory, grids are persistent),
         // so a level costs one graph launch instead of several hundred kernel launches.
         const int nBalls = p.states.nBalls;
+        if (p.nCand == 0) {   // an empty shard (more ranks than candidates): nothing to launch, the timer still closes
+            CK(cudaEventRecord(e->evStop, e->stream));
+            return BCU_OK;
+        }
         int64_t per = (p.nCand + e->pipeStreams - 1) / e->pipeStreams;
         if (per < 8192) per = 8192;
         if (per > PIPE_MAX_STRIKES) per = PIPE_MAX_STRIKES;
@@ -456,7 +490,7 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
                         pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, &ws);
                         ws.pruneMode = e->pruneMode;
                         CK(cudaStreamWaitEvent(e->pipeStream[g], e->pipeFork, 0));
-                        CK(launch_pipeline(e->dPipeParams.p + g, nBalls, e->table.nRails, e->table.nPockets, withCounters, ws, e->sms, e->pipeStream[g], true));
+                        CK(launch_pipeline(e->dPipeParams.p + g, nBalls, e->table.nRails, e->table.nPockets, withCounters, ws, e->sms, e->pipeStream[g], true, e->pipeCfg));
                         // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag
                         CK(cudaMemcpyAsync(e->hOverflow + g, pipeline_overflow_flag(ws), sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                            e->pipeStream[g]));
@@ -598,9 +632,10 @@ int bcu_evaluate_grid(bcu_engine* e, int32_t nDirs, int32_t nSpeeds, const float
     if (!e) return BCU_ERR_INVALID;
     if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate_grid: call bcu_set_states first");
     if (nDirs < 1 || nSpeeds < 1 || !dirs || !speeds) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: bad arguments");
+    if ((int64_t)nDirs * nSpeeds > INT32_MAX) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: n_dirs * n_speeds exceeds 2^31 - 1");
     const int64_t total = (int64_t)e->nStates * nDirs * nSpeeds;
     if (count < 0) count = total - first;
-    if (first < 0 || first + count > total) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: shard out of range");
+    if (first < 0 || count < 0 || first + count > total) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_grid: shard out of range");
     CK(cudaSetDevice(e->device));
     CK(e->dDirs.reserve((size_t)nDirs * 2)); CK(e->dSpeeds.reserve(nSpeeds));
     CK(cudaMemcpyAsync(e->dDirs.p, dirs, (size_t)nDirs * 2 * sizeof(float), cudaMemcpyHostToDevice, e->stream));
@@ -661,15 +696,34 @@ int bcu_topk(bcu_engine* e, int32_t k, uint64_t* outCost, uint64_t* outId, int32
 int bcu_simulate_trace(bcu_engine* e, int32_t nBalls, const float* pos, const int32_t* types, float vx, float vy,
                        int32_t* outLayers, float* outTimes, float* outRec) {
     if (!e || !pos || !types || !outLayers || !outTimes || !outRec) return BCU_ERR_INVALID;
+    if (nBalls < 1 || nBalls > MAX_BALLS) return fail(e, BCU_ERR_INVALID, "bcu_simulate_trace: bad ball count");
+    CK(cudaSetDevice(e->device));
+    // the strike's one-state table lives in its own buffers: the beam uploaded with bcu_set_states and the last launch
+    // (bcu_rerun / bcu_fetch_results / bcu_level_select) stay as they are -- except the per-strike result arrays, see below
     const uint32_t expected = 0xffffffffu;
-    int rc = bcu_set_states(e, 1, nBalls, pos, types, &expected, nullptr);
-    if (rc) return rc;
+    int8_t t8[MAX_BALLS];
+    for (int i = 0; i < nBalls; ++i) {
+        if (types[i] >= e->rules.nTypes) return fail(e, BCU_ERR_INVALID, "bcu_simulate_trace: type code out of range");
+        t8[i] = (int8_t)(types[i] < 0 ? -1 : types[i]);
+    }
+    CK(e->dTrPos.reserve((size_t)nBalls * 2)); CK(e->dTrType.reserve(nBalls)); CK(e->dTrExpected.reserve(1));
+    CK(cudaMemcpyAsync(e->dTrPos.p, pos, (size_t)nBalls * 2 * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaMemcpyAsync(e->dTrType.p, t8, nBalls, cudaMemcpyHostToDevice, e->stream));   // (pageable source: staged before return)
+    CK(cudaMemcpyAsync(e->dTrExpected.p, &expected, sizeof(expected), cudaMemcpyHostToDevice, e->stream));
+    int rc;
+    const int savedBalls = e->nBalls;
+    e->nBalls = nBalls;   // reserve_results / fill_common size the result arrays by it
     const int32_t s0 = 0;
     const uint64_t sc = 0, bc = 0;
     CK(e->dCandState.reserve(1)); CK(e->dVx.reserve(1)); CK(e->dVy.reserve(1)); CK(e->dSearchCost.reserve(1)); CK(e->dBaseCost.reserve(1));
     rc = reserve_results(e, 1, true, false);
-    if (rc) return rc;
-    CK(e->dTraceTimes.reserve(BCU_MAX_LAYERS)); CK(e->dTraceRec.reserve((size_t)BCU_MAX_LAYERS * nBalls * BCU_TRACE_REC));
+    if (rc) { e->nBalls = savedBalls; return rc; }
+    e->haveLast = false;   // the per-strike result arrays now hold the traced strike
+    if (e->dTraceTimes.reserve(BCU_MAX_LAYERS) != cudaSuccess ||
+        e->dTraceRec.reserve((size_t)BCU_MAX_LAYERS * nBalls * BCU_TRACE_REC) != cudaSuccess) {
+        e->nBalls = savedBalls;
+        return fail(e, BCU_ERR_CUDA, "bcu_simulate_trace: out of device memory");
+    }
     CK(cudaMemcpyAsync(e->dCandState.p, &s0, sizeof(s0), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dVx.p, &vx, sizeof(float), cudaMemcpyHostToDevice, e->stream));
     CK(cudaMemcpyAsync(e->dVy.p, &vy, sizeof(float), cudaMemcpyHostToDevice, e->stream));
@@ -677,10 +731,13 @@ int bcu_simulate_trace(bcu_engine* e, int32_t nBalls, const float* pos, const in
     CK(cudaMemcpyAsync(e->dBaseCost.p, &bc, sizeof(bc), cudaMemcpyHostToDevice, e->stream));
     LaunchParams p;
     fill_common(e, p, 1, true, false);
+    p.states.nStates = 1; p.states.nBalls = nBalls;
+    p.states.pos = e->dTrPos.p; p.states.type = e->dTrType.p; p.states.expectedMask = e->dTrExpected.p;
     p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
     p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
     p.out.traceTimes = e->dTraceTimes.p; p.out.traceRec = e->dTraceRec.p;
     rc = run(e, p, true);
+    e->nBalls = savedBalls;
     if (rc) return rc;
     uint32_t flags = 0;
     CK(cudaMemcpyAsync(&flags, e->dFlags.p, sizeof(flags), cudaMemcpyDeviceToHost, e->stream));
@@ -735,16 +792,24 @@ int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* outPos, uin
     if (!e) return BCU_ERR_INVALID;
     if (!e->haveLast || !e->last.out.finalPos) return fail(e, BCU_ERR_STATE, "bcu_gather: no launch with final positions");
     if (n < 0 || (n > 0 && !ids)) return fail(e, BCU_ERR_INVALID, "bcu_gather: bad arguments");
+    if (n == 0) return BCU_OK;
     CK(cudaSetDevice(e->device));
-    // few (<= 1024) records: one small copy per record keeps this path kernel-free
     const int NB = e->nBalls;
     for (int32_t i = 0; i < n; ++i) {
         const int64_t local = (int64_t)ids[i] - e->lastFirst;
         if (local < 0 || local >= e->last.nCand) return fail(e, BCU_ERR_INVALID, "bcu_gather: id not in the last launch");
-        if (outPos) CK(cudaMemcpyAsync(outPos + (size_t)i * NB * 2, e->dFinalPos.p + (size_t)local * NB * 2, NB * 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
-        if (outPotted) CK(cudaMemcpyAsync(outPotted + i, e->dPotted.p + local, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
-        if (outTime) CK(cudaMemcpyAsync(outTime + i, e->dFinalTime.p + local, sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     }
+    // one kernel gathers the n records into a record block (the beam's own pack kernel), three copies bring it back
+    const size_t bb = record_block_bytes(n, NB);
+    CK(e->dGatherIds.reserve(n)); CK(e->dGatherPos.reserve((bb + 3) / 4));
+    CK(cudaMemcpyAsync(e->dGatherIds.p, ids, (size_t)n * sizeof(uint64_t), cudaMemcpyHostToDevice, e->stream));
+    CK(launch_pack_records(e->dGatherIds.p, e->dGatherIds.p, n, e->lastFirst, e->dPotted.p, e->dFinalTime.p, e->dFinalPos.p, NB,
+                           e->dGatherPos.p, e->stream));
+    e->launches += 1;
+    const char* blk = (const char*)e->dGatherPos.p;
+    if (outPotted) CK(cudaMemcpyAsync(outPotted, blk + (size_t)n * 16, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (outTime) CK(cudaMemcpyAsync(outTime, blk + (size_t)n * 20, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (outPos) CK(cudaMemcpyAsync(outPos, blk + (size_t)n * 24, (size_t)n * NB * 8, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return BCU_OK;
 }
@@ -766,7 +831,7 @@ int bcu_level_select(bcu_engine* e, int32_t k) {
     if (k < 1 || k > 1024) return fail(e, BCU_ERR_INVALID, "bcu_level_select: k must be in 1..1024");
     CK(cudaSetDevice(e->device));
     // BCU_SELECT_TIMING=1 (diagnosis only): CUDA events between the phases, times on stderr
-    static const bool timing = getenv("BCU_SELECT_TIMING") != nullptr;
+    const bool timing = e->selectTiming;
     cudaEvent_t tv[5] = {};
     int nt = 0;
     auto mark = [&]() { if (timing && nt < 5) { cudaEventCreate(&tv[nt]); cudaEventRecord(tv[nt], e->stream); ++nt; } };
@@ -956,6 +1021,33 @@ int bcu_enable_counters(bcu_engine* e, int enable) {
 int bcu_set_prune(bcu_engine* e, int mode) {
     if (!e || mode < 0 || mode > 2) return BCU_ERR_INVALID;
     e->pruneMode = mode;
+    return BCU_OK;
+}
+
+int bcu_get_prune(const bcu_engine* e) { return e ? e->pruneMode : -1; }
+
+// Test hook: the multi-GPU merge kernel on host-supplied record blocks (what ncclAllGather delivers on a multi-GPU run),
+// so that merge_records_kernel is covered on a single GPU.
+int bcu_test_merge_records(bcu_engine* e, int32_t nBlocks, int32_t k, int32_t nBalls, const void* blocks, void* outBlock) {
+    if (!e) return BCU_ERR_INVALID;
+    if (nBlocks < 1 || nBlocks > 64 || k < 1 || k > 1024 || nBalls < 1 || nBalls > MAX_BALLS || !blocks || !outBlock)
+        return fail(e, BCU_ERR_INVALID, "bcu_test_merge_records: bad arguments");
+    CK(cudaSetDevice(e->device));
+    const size_t bb = record_block_bytes(k, nBalls);
+    DevBuf<unsigned char> dIn, dOut;
+    cudaError_t ce;
+    if ((ce = dIn.reserve(bb * nBlocks)) != cudaSuccess || (ce = dOut.reserve(bb)) != cudaSuccess) {
+        dIn.release(); dOut.release();
+        e->err = std::string("bcu_test_merge_records: ") + cudaGetErrorString(ce);
+        return BCU_ERR_CUDA;
+    }
+    ce = cudaMemcpyAsync(dIn.p, blocks, bb * nBlocks, cudaMemcpyHostToDevice, e->stream);
+    if (ce == cudaSuccess) ce = launch_merge_records(dIn.p, nBlocks, k, nBalls, dOut.p, e->stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(outBlock, dOut.p, bb, cudaMemcpyDeviceToHost, e->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+    e->launches += 2;
+    dIn.release(); dOut.release();
+    if (ce != cudaSuccess) { e->err = std::string("bcu_test_merge_records: ") + cudaGetErrorString(ce); return BCU_ERR_CUDA; }
     return BCU_OK;
 }
 

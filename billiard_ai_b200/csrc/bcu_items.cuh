@@ -116,6 +116,9 @@ constexpr float PRUNE_MIN_QREL = PRUNE_MIN_QREL_V;   // |depressed q's numerator
 constexpr float PRUNE_MIN_LEADING = PRUNE_MIN_LEADING_V;   // m^2/s^4; moving-vs-resting pairs have 4.87e-3 (rolling) or 0.70 (sliding)
 constexpr float PRUNE_MIN_SIN_SQ = PRUNE_MIN_SIN_SQ_V;
 constexpr uint32_t JOB_MARK = 0x80000000u;
+#ifndef PRUNE_REST_PASS_ONLY_V
+#define PRUNE_REST_PASS_ONLY_V 1   // 0: apply the bound to every resting partner (a weakened build the regression vectors must catch)
+#endif
 #ifndef PARTNER_BATCH_V
 #define PARTNER_BATCH_V 11
 #endif
@@ -324,7 +327,11 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                     if (!(dist > dd)) {
                         bool skip = false;
                         if (prune) {
+#if PRUNE_REST_PASS_ONLY_V
                             if (distSq <= passMaxSq) skip = distSq > reachSq;   // passed completely before the turning point
+#else
+                            skip = distSq > reachSq;   // guard variant for tests/golden/prune_regressions.json: NOT sound
+#endif
                         }
                         if (skip) {
                             ++skipped;

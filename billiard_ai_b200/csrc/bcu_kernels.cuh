@@ -86,11 +86,20 @@ struct PipeWorkspace {
     int pdlEarly;              // kernels signal cudaTriggerProgrammaticLaunchCompletion() at once (launch_pipeline)
     int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
 };
+// Per-engine launch configuration of the pipeline (no process-wide state: two engines on two devices or threads each
+// own one).  Filled by bcu_create from the BCU_* environment; the occupancy figures are computed on first use for the
+// engine's device and the shared-memory size of its ball count.
+struct PipeLaunchCfg {
+    int occItems = 0, occQuartic = 0, occApply = 0;
+    size_t occSmem = ~(size_t)0;
+    int pdlMode = 1;           // BCU_PDL: 0 off, 1 programmatic dependent launch, 2 + early trigger
+    bool roundTiming = false;  // BCU_ROUND_TIMING (diagnosis): CUDA events around every kernel, times on stderr
+};
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
 void pipeline_upload_constants(cudaStream_t stream);
 cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, int nRails, int nPockets, bool withCounters,
-                            const PipeWorkspace& w, int sms, cudaStream_t stream, bool resetOverflow);
+                            const PipeWorkspace& w, int sms, cudaStream_t stream, bool resetOverflow, PipeLaunchCfg& cfg);
 int pipeline_launch_count();
 
 void upload_constants(cudaStream_t stream);   // physics constants only (identical for every engine)

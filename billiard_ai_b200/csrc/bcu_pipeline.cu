@@ -569,7 +569,7 @@ int pipeline_launch_count() { return 2 + 3 * ROUNDS; }
 // from memory, so a captured CUDA graph of this sequence stays valid from call to call); all grids are persistent and
 // sized by the workspace capacity, so nothing in the launch sequence depends on the candidate count.
 cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int nPockets, bool withCounters,
-                            const PipeWorkspace& wsIn, int sms, cudaStream_t stream, bool resetOverflow) {
+                            const PipeWorkspace& wsIn, int sms, cudaStream_t stream, bool resetOverflow, PipeLaunchCfg& cfg) {
     PipeWorkspace w = wsIn;
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
@@ -580,15 +580,15 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     (void)nRails; (void)nPockets;
     const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
     // BCU_ROUND_TIMING=1 (diagnosis only): CUDA events around every kernel, per-round times on stderr
-    static const bool timing = getenv("BCU_ROUND_TIMING") != nullptr;
+    const bool timing = cfg.roundTiming;
     std::vector<cudaEvent_t> ev;
     auto mark = [&]() {
         if (!timing) return;
         cudaEvent_t x; cudaEventCreate(&x); cudaEventRecord(x, stream); ev.push_back(x);
     };
     // persistent grids: exactly one resident wave of every kernel
-    static int occItems = 0, occQuartic = 0, occApply = 0;
-    static size_t occSmem = ~(size_t)0;
+    int& occItems = cfg.occItems; int& occQuartic = cfg.occQuartic; int& occApply = cfg.occApply;
+    size_t& occSmem = cfg.occSmem;
     if (occSmem != itemSmem) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occItems, items_kernel, ITEM_BLOCK, itemSmem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occQuartic, quartic_kernel, QUARTIC_BLOCK, 0);
@@ -602,7 +602,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // cudaTriggerProgrammaticLaunchCompletion() at once, so the CTAs of kernel k+1 are placed (and run their prologue: table
     // geometry to shared memory) while kernel k drains; they read nothing kernel k writes before cudaGridDependencySynchronize().
     // A round is three latency-bound kernels, so launch gaps are a visible share of a level.  BCU_NO_PDL=1 switches it off.
-    static const int pdlMode = getenv("BCU_PDL") ? atoi(getenv("BCU_PDL")) : 1;
+    const int pdlMode = cfg.pdlMode;
     const bool pdl = pdlMode > 0;
     w.pdlEarly = pdlMode > 1;
     cudaLaunchAttribute attr[1];
@@ -616,6 +616,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     };
     mark();
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
     mark();
     for (int r = 0; r < ROUNDS; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * occItems, ITEM_BLOCK, itemSmem);

@@ -66,6 +66,8 @@ def load_library(path=None):
     lib.bcu_destroy.restype = None
     lib.bcu_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     lib.bcu_host_free.argtypes = [C.c_void_p]
+    lib.bcu_get_prune.argtypes = [C.c_void_p]
+    lib.bcu_test_merge_records.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     if path is None:
         _lib = lib
     return lib
@@ -118,8 +120,8 @@ class _LazyResults(dict):
 class Engine:
     """One engine = one CUDA device + one stream + the table / rules constants."""
 
-    def __init__(self, rails6, pockets3, ball_radius, scores, cue_type=0, device=0):
-        self.lib = load_library()
+    def __init__(self, rails6, pockets3, ball_radius, scores, cue_type=0, device=0, lib_path=None):
+        self.lib = load_library(lib_path)   # lib_path: a tuning / guard-variant build (billiard_ai_b200/build.py)
         self._rails = np.ascontiguousarray(rails6, dtype=np.float32)
         self._pockets = np.ascontiguousarray(np.asarray(pockets3, dtype=np.float32)[:, :3])
         self._scores = np.ascontiguousarray(scores, dtype=np.float64)
@@ -140,13 +142,13 @@ class Engine:
         self._result_cache = {}
 
     @classmethod
-    def from_table(cls, tbl, scores, cue_type=0, device=0):
+    def from_table(cls, tbl, scores, cue_type=0, device=0, lib_path=None):
         """tbl: dict in the layout of tests/golden/table.json (reference configuration.json)."""
         rails6 = np.array([[r["start"][0], r["start"][1], r["end"][0], r["end"][1], r["shift"][0], r["shift"][1]]
                            for r in tbl["rails"]], dtype=np.float32)
         pockets3 = np.array([[p["position"][0], p["position"][1], p["radius"]] for p in tbl["pockets"]],
                             dtype=np.float32)
-        return cls(rails6, pockets3, tbl["ballRadius"], scores, cue_type, device)
+        return cls(rails6, pockets3, tbl["ballRadius"], scores, cue_type, device, lib_path=lib_path)
 
     def close(self):
         if getattr(self, "h", None):
@@ -355,7 +357,6 @@ class Engine:
         self._ck(self.lib.bcu_simulate_trace(self.h, C.c_int32(n), _p(pos, C.c_float), _p(types, C.c_int32),
                                              C.c_float(vx), C.c_float(vy), C.byref(nl), _p(times, C.c_float),
                                              _p(rec, C.c_float)), "bcu_simulate_trace")
-        self.n_states, self.n_balls = 1, n
         return nl.value, times[:nl.value], rec[:nl.value]
 
     def trace_strikes(self, cand_state, vx, vy):
@@ -404,8 +405,23 @@ class Engine:
         return dict(zip(["events", "pair_items", "quartics", "rail_items", "pocket_items"], out.tolist()))
 
     def set_prune(self, mode):
-        """0 off, 1 on (default), 2 audit; see include/billiard_cuda.h."""
+        """0 off (default: every quartic the reference solves is solved), 1 on (opt-in: audited, not proven), 2 audit;
+        see include/billiard_cuda.h."""
         self._ck(self.lib.bcu_set_prune(self.h, C.c_int(int(mode))), "bcu_set_prune")
+
+    def get_prune(self):
+        return int(self.lib.bcu_get_prune(self.h))
+
+    def test_merge_records(self, blocks, k, n_balls):
+        """Test hook: G host record blocks (uint8 arrays, layout of distributed.view_block) -> the merged block, computed
+        by the device merge kernel that bcu_level_select runs after the all-gather."""
+        blocks = [np.ascontiguousarray(b, dtype=np.uint8) for b in blocks]
+        cat = np.ascontiguousarray(np.concatenate(blocks))
+        out = np.zeros(len(blocks[0]), np.uint8)
+        self._ck(self.lib.bcu_test_merge_records(self.h, C.c_int32(len(blocks)), C.c_int32(k), C.c_int32(n_balls),
+                                                 cat.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)),
+                 "bcu_test_merge_records")
+        return out
 
     def prune_counters(self):
         out = np.zeros(2, np.uint64)

@@ -8,9 +8,12 @@
  * :1473-1532 simulationCost, rules billiard_snooker.cpp:787-790, 1128-1153) it replaces.
  * The C++ mirror of those entry points that calls this ABI lives in billiard_ai_b200/host/.
  *
- * Conventions: POD only, caller-owned buffers, no globals, one CUDA stream per engine, every call
- * returns a bcu_status (0 = OK).  There is NO CPU fallback: if no CUDA device is usable,
- * bcu_create fails with BCU_ERR_NO_DEVICE.
+ * Conventions: POD only, caller-owned buffers, one CUDA stream per engine, every call returns a bcu_status (0 = OK).
+ * Thread-compatible: all state lives in the engine (launch configuration, occupancy figures, staging buffers), so
+ * different engines may be used from different threads and on different devices at the same time; one engine must not
+ * be used from two threads at once.  The only process-wide state is the function table of the dlopen'ed NCCL library
+ * (filled once under a lock).  There is NO CPU fallback: if no CUDA device is usable, bcu_create fails with
+ * BCU_ERR_NO_DEVICE.
  */
 #ifndef BILLIARD_CUDA_H
 #define BILLIARD_CUDA_H
@@ -130,7 +133,10 @@ int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* out_pos, ui
 /* ---- single strike with the full layer trace (reference public simulate(), billiard_search.cpp:141-175) --
  * pos [n_balls][2], types [n_balls]; out_times [32]; out_rec [32][n_balls][10]:
  *   {node kind, after.pos.xy, after.vel.xy, after.isRolling, before.vel.xy, cause index, -1}
- * *out_layers = number of layers, 0 when the reference would return nullopt. */
+ * *out_layers = number of layers, 0 when the reference would return nullopt.
+ * The strike's state is uploaded into buffers of its own: the states of the last bcu_set_states stay in place.  The
+ * per-strike result arrays of the last launch are overwritten (bcu_fetch_results / bcu_topk / bcu_rerun need a new
+ * launch afterwards); a beam selected with bcu_level_select stays valid. */
 int bcu_simulate_trace(bcu_engine* e, int32_t n_balls, const float* pos, const int32_t* types, float vx, float vy,
                        int32_t* out_layers, float* out_times, float* out_rec);
 
@@ -209,11 +215,24 @@ int bcu_get_counters(bcu_engine* e, uint64_t* out5);
 /* Reach bound on ball pairs: a pair whose centre distance exceeds what the two balls can cover
  * before the strike's best event time so far cannot produce the next event (the reference would solve its quartic,
  * billiard_physics.cpp:283-381, and discard the result in min(), billiard_search.cpp:2002-2013), so it is not solved.
- * mode 0: off (every quartic the reference solves is solved); 1: on (default); 2: audit -- everything is solved and the
- * jobs the bound would have skipped are checked: out2 = {pairs skipped or marked, marked jobs whose result would have
- * mattered}; the second number must be 0.  Counters need bcu_enable_counters(e, 1). */
+ * mode 0 (DEFAULT): off -- every test the reference makes is made and every quartic it solves is solved; parity with the
+ *         reference follows from construction.
+ * mode 1: on (opt-in, for throughput).  The bound is a theorem about the roots of the collision polynomial plus an
+ *         EMPIRICAL characterisation of where the reference's closed-form solver returns them:
+ *         audited on > 8e8 random strikes with no differing result, not proven.  Also enables the division-free rail /
+ *         pocket / partner filters and the per-line candidate cache, which are conservative by construction.
+ * mode 2: audit -- everything is solved and the jobs the bound would have skipped are checked: out2 = {pairs skipped or
+ *         marked, marked jobs whose result would have mattered}; the second number must be 0.
+ * Counters need bcu_enable_counters(e, 1).  $BCU_PRUNE overrides the default at bcu_create. */
 int bcu_set_prune(bcu_engine* e, int mode);
+int bcu_get_prune(const bcu_engine* e);
 int bcu_get_prune_counters(bcu_engine* e, uint64_t* out2);
+/* Test hook: runs the multi-GPU merge kernel (bcu_level_select's step after ncclAllGather) on n_blocks record blocks
+ * supplied by the host -- each k entries for n_balls balls, layout
+ *   cost u64[k] | id u64[k] | potted u32[k] | time f32[k] | pos f32[k][n_balls][2], entries past the valid count cost = id = ~0,
+ * every block ascending by (cost, id) -- and returns the merged block (same layout).  Lets a one-GPU test cover the
+ * kernel that otherwise only runs with more than one rank. */
+int bcu_test_merge_records(bcu_engine* e, int32_t n_blocks, int32_t k, int32_t n_balls, const void* blocks, void* out_block);
 /* number of kernels launched by this engine so far */
 int64_t bcu_launch_count(const bcu_engine* e);
 

@@ -22,8 +22,7 @@ SRC = os.path.join(ROOT, "tests", "host_harness.cpp")
 OUT = os.path.join(ROOT, "tests", "_build", "libhost_harness.so")
 
 
-@pytest.fixture(scope="module")
-def hh():
+def _load_harness():
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     deps = [SRC] + [os.path.join(ROOT, "billiard_ai_b200", "csrc", f)
                     for f in os.listdir(os.path.join(ROOT, "billiard_ai_b200", "csrc")) if f.endswith((".cuh", ".inc"))]
@@ -34,6 +33,11 @@ def hh():
     lib.hh_fallback_count.restype = C.c_longlong
     lib.hh_fallback_count(1)
     return lib
+
+
+@pytest.fixture(scope="module")
+def hh():
+    return _load_harness()
 
 
 def _P(a):
@@ -74,6 +78,24 @@ CASES = [
     ("hypot", 6, lambda r: (r.uniform(-1, 1, N) * 10.0 ** r.uniform(-10, 10, N),
                             r.uniform(-1, 1, N) * 10.0 ** r.uniform(-10, 10, N))),
 ]
+
+
+def check_libm_functions(n):
+    """Every case above on n arguments each (used by the GPU tier to check the box's own glibc)."""
+    global N
+    lib = _load_harness()
+    saved, N = N, n
+    try:
+        for name, which, gen in CASES:
+            x, y = gen(np.random.RandomState(77 + which * 17 + len(name)))
+            lib.hh_fallback_count(1)
+            (a, a2), (b, b2) = _both(lib, which, x, y)
+            assert lib.hh_fallback_count(1) == 0, name
+            assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), name
+            if which == 5:
+                assert np.array_equal(a2.view(np.uint64), b2.view(np.uint64)), name
+    finally:
+        N = saved
 
 
 @pytest.mark.parametrize("name,which,gen", CASES, ids=[c[0] for c in CASES])
