@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libbilliard_cuda.so")
-SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu", "bcu_rules.cpp"]
+SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu", "bcu_rules.cpp", "bcu_search.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
@@ -62,7 +62,7 @@ def build(force=False, verbose=False, extra=()):
     for cmd, pr in procs:
         if pr.wait() != 0:
             raise subprocess.CalledProcessError(pr.returncode, cmd)
-    subprocess.check_call([nvcc_path(), "-shared", "-o", OUT] + objs + ["-ldl"])
+    subprocess.check_call([nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT] + objs + ["-ldl"])
     return OUT
 
 
@@ -103,7 +103,7 @@ def build_variants(names=None, force=False):
         if pr.wait() != 0:
             raise subprocess.CalledProcessError(pr.returncode, cmd)
         others = [os.path.join(OBJDIR, os.path.splitext(s)[0] + ".o") for s in SOURCES if s != "bcu_pipeline.cu"]
-        subprocess.check_call([nvcc_path(), "-shared", "-o", variant_path(name), obj] + others + ["-ldl"])
+        subprocess.check_call([nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", variant_path(name), obj] + others + ["-ldl"])
     return {n: variant_path(n) for n in names}
 
 

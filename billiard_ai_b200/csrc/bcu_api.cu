@@ -1073,4 +1073,11 @@ int bcu_get_counters(bcu_engine* e, uint64_t* out5) {
 
 int64_t bcu_launch_count(const bcu_engine* e) { return e ? e->launches : 0; }
 
+int bcu_engine_rank_info(const bcu_engine* e, int32_t* outRank, int32_t* outRanks) {
+    if (!e) return BCU_ERR_INVALID;
+    if (outRank) *outRank = e->rank;
+    if (outRanks) *outRanks = e->nRanks;
+    return BCU_OK;
+}
+
 }  // extern "C"

@@ -68,6 +68,9 @@ def load_library(path=None):
     lib.bcu_host_free.argtypes = [C.c_void_p]
     lib.bcu_get_prune.argtypes = [C.c_void_p]
     lib.bcu_test_merge_records.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.bcu_engine_rank_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.bcu_search_levels.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p,
+                                      C.c_void_p]
     if path is None:
         _lib = lib
     return lib
@@ -430,3 +433,9 @@ class Engine:
 
     def launch_count(self):
         return int(self.lib.bcu_launch_count(self.h))
+
+    def rank_info(self):
+        """(rank, number of ranks) of the engine's communicator."""
+        r, n = C.c_int32(0), C.c_int32(1)
+        self._ck(self.lib.bcu_engine_rank_info(self.h, C.byref(r), C.byref(n)), "bcu_engine_rank_info")
+        return r.value, n.value

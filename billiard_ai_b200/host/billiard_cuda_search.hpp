@@ -14,16 +14,35 @@
 //        == one SIMULATION node per candidate: simulate(node, state, mustBeValid) + simulationCost + rules
 //           (billiard_search.cpp:1358-1471, 1473-1532), returning cost / validity / end state per candidate.
 //
+//   billiard::search::cuda::search(state, search, solutions, config)
+//        == billiard::search::search(const State&, const Search&, uint16_t, const Configuration&)
+//           billiard_search.hpp:9-12, src/billiard_search.cpp:74-98: same arguments, same result type
+//           (std::future<std::vector<std::vector<node::System>>>: outer vector ascending by cost, inner vector one System
+//           per break, type.hpp:525-537), same ways to end (enough solutions / 10 000 ms / no work left,
+//           process.hpp:188-198), a newer request replaces the one in flight (process.hpp:82-83).  The geometric planner
+//           stays the reference's own expand() on the host (billiard_search.cpp:224-244); every SIMULATION node it emits
+//           is evaluated on the device in batches instead of one by one on the CPU (:1358-1471), the rules between
+//           breaks are the Configuration's own std::functions (:1407-1462).  See SearchFront below.
+//
 // Errors: a failing bcu_* call throws std::runtime_error with bcu_last_error(); there is no CPU fallback.
 #pragma once
 
 #include <billiard_physics/billiard_physics.hpp>
 #include <billiard_search/type.hpp>
 
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <cstdint>
+#include <future>
+#include <memory>
+#include <mutex>
 #include <optional>
+#include <queue>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <utility>
 #include <vector>
@@ -133,8 +152,9 @@ public:
     }
 
     // device trace (include/billiard_cuda.h: bcu_simulate_trace) -> the reference's node::System
-    std::optional<node::System> systemFromTrace(const State& state, int layers, const float* times, const float* rec) {
-        const int n = (int)state._balls.size();
+    // `slots` > 0: the trace was made on a frame padded to that many ball slots (slots past the State's balls are empty)
+    std::optional<node::System> systemFromTrace(const State& state, int layers, const float* times, const float* rec, int slots = 0) {
+        const int n = slots > 0 ? slots : (int)state._balls.size();
         if (layers == 0) return std::nullopt;  // billiard_search.cpp:170-174
         const float al = physics::accelerationLength(), sl = physics::slideAccelerationLength();
         node::System system;
@@ -143,8 +163,8 @@ public:
             std::unordered_map<std::string, node::Node> nodes;
             for (int b = 0; b < n; ++b) {
                 const float* r = &rec[((size_t)l * n + b) * BCU_TRACE_REC];
+                if (r[0] < 0.0f || b >= (int)state._balls.size()) continue;  // no such ball
                 const Ball& ball = state._balls[b];
-                if (r[0] < 0.0f) continue;  // no such ball
                 {
                     // createLayer copies the nodes of static balls (at rest / potted) unchanged (billiard_search.cpp:1965-1966)
                     const auto staticType = (node::NodeType)(int)r[0];
@@ -230,6 +250,8 @@ public:
     }
 
     bcu_engine* handle() { return _e; }
+    const RulesTable& rules() const { return _rules; }
+    void checked(int rc, const char* what) const { check(rc, what); }
 
 private:
     void flatten(const State& state, std::vector<float>& pos, std::vector<int32_t>& types) const {
@@ -247,5 +269,396 @@ private:
     RulesTable _rules;
     std::vector<std::string> _railIds, _pocketIds;
 };
+
+}  // namespace billiard::search::cuda
+
+// ---- the search() drop-in ---------------------------------------------------------------------------------------------
+// Internals of the reference's billiard_search.cpp with external linkage (declared there at :42-49, defined :100-120,
+// 224-297): the planner and the request check are the reference's own code, called, not restated.
+namespace billiard::search {
+std::vector<std::shared_ptr<SearchNode>> expand(const std::shared_ptr<SearchNode>& input, const std::shared_ptr<SearchState>& config);
+std::vector<std::shared_ptr<SearchNode>> addPocketsAsInitialTargets(const State& state, const Search& search, const Configuration& config);
+bool isValidSearch(const State& state, const Search& search);
+}  // namespace billiard::search
+
+namespace billiard::search::cuda {
+
+struct SearchOptions {
+    int device = 0;
+    int breaks = 2;                  // BREAKS, billiard_search.cpp:15
+    uint64_t maxDurationMs = 10000;  // ProcessManager::process default, process.hpp:80
+    size_t batch = 256;              // SIMULATION nodes collected before a device launch (the planner runs ahead this far)
+    int prune = 0;                   // bcu_set_prune mode (0: every quartic the reference solves is solved)
+};
+
+struct SearchReport {   // what the last finished request did (diagnosis / tests)
+    size_t expansions = 0, simulations = 0, batches = 0, solutions = 0;
+    bool enoughSolutions = false, noTimeLeft = false, noWork = false, cancelled = false;
+    double ms = 0.0;
+    std::vector<uint64_t> costs;   // accumulated cost of every solution returned, in the order of the result
+};
+
+// == process::ProcessManager<std::shared_ptr<SearchNode>, SearchState, std::vector<node::System>> for this path
+// (lib/process/include/process/process.hpp): process() returns a future and replaces the request in flight (:79-98: the
+// replaced request's promise is dropped, so its future reports std::future_errc::broken_promise exactly as the
+// reference's does); one worker thread pops nodes in ascending cost (:19-25), SEARCH nodes are expanded by the reference's
+// planner, SIMULATION nodes are collected and evaluated on the device `batch` at a time; the request ends when enough
+// solutions are final, its time is up or no work is left (:188-198), and all solutions found come back ascending.
+// "Enough" is exact here: the request ends once `solutions` solutions are final AND no open node is cheaper than the
+// last of them (costs only grow along a path), so the first `solutions` entries are the cheapest that exist -- what the
+// reference's best-first order approaches but, with worker threads syncing every 100 ms, does not guarantee.
+class SearchFront {
+public:
+    using Result = std::vector<std::vector<node::System>>;
+
+    explicit SearchFront(SearchOptions options = {}) : _options(options), _worker([this] { work(); }) {}
+    ~SearchFront() {
+        {
+            std::lock_guard<std::mutex> guard(_lock);
+            _exit = true;
+            _cancel = true;
+        }
+        _wake.notify_all();
+        _worker.join();
+    }
+    SearchFront(const SearchFront&) = delete;
+    SearchFront& operator=(const SearchFront&) = delete;
+
+    std::future<Result> process(const State& state, const Search& search, uint16_t solutions, const Configuration& config) {
+        auto request = std::make_unique<Request>(Request{state, search, solutions, config, std::promise<Result>{}});
+        std::future<Result> future = request->result.get_future();
+        {
+            std::lock_guard<std::mutex> guard(_lock);
+            _pending = std::move(request);   // a request still waiting is dropped here (broken promise), one in flight is cancelled
+            _cancel = true;
+        }
+        _wake.notify_all();
+        return future;
+    }
+
+    SearchReport lastReport() {
+        std::lock_guard<std::mutex> guard(_lock);
+        return _report;
+    }
+
+private:
+    struct Request {
+        State state;
+        Search search;
+        uint16_t solutions;
+        Configuration config;
+        std::promise<Result> result;
+    };
+    struct Open {
+        std::shared_ptr<SearchNode> node;
+        uint64_t order;
+    };
+    struct Later {   // process::Comparator (ascending _cost), creation order breaks ties: deterministic
+        bool operator()(const Open& a, const Open& b) const {
+            return a.node->_cost != b.node->_cost ? a.node->_cost > b.node->_cost : a.order > b.order;
+        }
+    };
+    struct Frame {   // the table one break is played on: the _state of the break's root SEARCH node, in a fixed slot order
+        State state{std::vector<Ball>{}};
+        std::vector<std::string> searched;   // getTypeOf(search, state), billiard_search.cpp:1994-2000
+    };
+
+    void work() {
+        for (;;) {
+            std::unique_ptr<Request> request;
+            {
+                std::unique_lock<std::mutex> guard(_lock);
+                _wake.wait(guard, [this] { return _exit || _pending; });
+                if (_exit) return;
+                request = std::move(_pending);
+                _cancel = false;
+            }
+            try {
+                SearchReport report;
+                Result result = run(*request, report);
+                std::lock_guard<std::mutex> guard(_lock);
+                _report = report;
+                if (!report.cancelled) request->result.set_value(std::move(result));
+                // cancelled: the promise dies with the request -> broken_promise, as in the reference
+            } catch (...) {
+                request->result.set_exception(std::current_exception());
+            }
+        }
+    }
+
+    bool cancelled() {
+        std::lock_guard<std::mutex> guard(_lock);
+        return _cancel;
+    }
+
+    // the engine is kept across requests and rebuilt when the table or the ball types change
+    Engine& engineFor(const Configuration& config, const std::vector<std::string>& typeNames) {
+        std::vector<float> key{config._ball._radius};
+        for (auto& kv : config._table._rails) {
+            const Rail& r = kv.second;
+            key.insert(key.end(), {r._normal.x, r._normal.y, r._shiftedStart.x, r._shiftedStart.y, r._shiftedEnd.x, r._shiftedEnd.y});
+        }
+        for (auto& p : config._table._pockets) key.insert(key.end(), {p._position.x, p._position.y, p._radius});
+        RulesTable rules = RulesTable::fromConfiguration(config, typeNames);
+        for (double sc : rules.scores) key.push_back((float)sc);
+        if (!_engine || key != _engineKey || typeNames != _engine->rules().typeNames) {
+            _engine.reset();
+            _engine = std::make_unique<Engine>(config, rules, _options.device);
+            _engine->checked(bcu_set_prune(_engine->handle(), _options.prune), "bcu_set_prune");
+            _engineKey = key;
+        }
+        return *_engine;
+    }
+
+    static std::vector<std::string> typeNamesOf(const State& state) {
+        std::vector<std::string> names{"WHITE"};
+        for (auto& b : state._balls)
+            if (std::find(names.begin(), names.end(), b._type) == names.end()) names.push_back(b._type);
+        std::sort(names.begin() + 1, names.end());
+        return names;
+    }
+
+    static const SearchNode* breakRoot(const SearchNode* simulation) {
+        const SearchNode* node = simulation->_parent.get();
+        while (node->_parent && node->_parent->_type == SearchNodeType::SEARCH) node = node->_parent.get();
+        return node;
+    }
+
+    Result run(Request& rq, SearchReport& report) {
+        using clock = std::chrono::steady_clock;
+        const auto t0 = clock::now();
+        auto elapsedMs = [&] { return std::chrono::duration<double, std::milli>(clock::now() - t0).count(); };
+        Result result;
+        if (!isValidSearch(rq.state, rq.search)) return result;   // billiard_search.cpp:78-84
+        const Configuration& config = rq.config;
+        Engine& engine = engineFor(config, typeNamesOf(rq.state));
+        const RulesTable& rules = engine.rules();
+        auto searchState = std::make_shared<SearchState>(SearchState{config});   // :92-94
+        searchState->_ball._accelerationLength = physics::accelerationLength();
+        searchState->_ball._slideAccelerationLength = physics::slideAccelerationLength();
+
+        std::priority_queue<Open, std::vector<Open>, Later> open;
+        uint64_t order = 0;
+        for (auto& node : addPocketsAsInitialTargets(rq.state, rq.search, config)) open.push(Open{node, order++});
+        std::vector<Open> solutions;   // SIMULATION nodes with _isSolution, _cost = accumulated cost
+        std::unordered_map<const SearchNode*, std::shared_ptr<Frame>> frames;   // by break root
+        auto frameOf = [&](const SearchNode* root) -> std::shared_ptr<Frame> {
+            auto it = frames.find(root);
+            if (it != frames.end()) return it->second;
+            auto frame = std::make_shared<Frame>();
+            auto asSearch = root->asSearch();
+            for (auto& kv : asSearch->_state) frame->state._balls.push_back(kv.second);
+            std::sort(frame->state._balls.begin(), frame->state._balls.end(), [](const Ball& a, const Ball& b) { return a._id < b._id; });
+            if (!asSearch->_search._types.empty()) frame->searched = asSearch->_search._types;
+            else if (asSearch->_state.count(asSearch->_search._id)) frame->searched = {asSearch->_state.at(asSearch->_search._id)._type};
+            frames.insert({root, frame});
+            return frame;
+        };
+        auto kthCost = [&]() -> uint64_t {   // cost of the `solutions`-th cheapest solution so far
+            if (rq.solutions == 0) return 0ull;   // the reference's `_solutions.size() >= _minimalSolutions` holds at once
+            if (solutions.size() < rq.solutions) return ~0ull;
+            std::vector<uint64_t> costs;
+            for (auto& s : solutions) costs.push_back(s.node->_cost);
+            std::nth_element(costs.begin(), costs.begin() + (rq.solutions - 1), costs.end());
+            return costs[rq.solutions - 1];
+        };
+
+        std::vector<std::shared_ptr<SearchNode>> batch;
+        for (;;) {
+            // ---- the planner runs ahead: SEARCH nodes are expanded in ascending cost, SIMULATION nodes collected ------------
+            batch.clear();
+            const uint64_t bound = kthCost();
+            while (!open.empty() && batch.size() < _options.batch) {
+                if ((report.expansions & 63) == 0) {
+                    if (cancelled()) { report.cancelled = true; break; }
+                    if (elapsedMs() >= (double)_options.maxDurationMs) { report.noTimeLeft = true; break; }
+                }
+                if (open.top().node->_cost >= bound) { report.enoughSolutions = true; break; }
+                auto node = open.top().node;
+                open.pop();
+                report.expansions++;
+                if (node->_type == SearchNodeType::SEARCH) {
+                    for (auto& child : expand(node, searchState)) open.push(Open{child, order++});
+                } else {
+                    batch.push_back(node);
+                }
+            }
+            if (report.cancelled) return result;
+            if (batch.empty()) {
+                report.noWork = open.empty() && !report.noTimeLeft && !report.enoughSolutions;
+                break;
+            }
+            // ---- one device launch for the batch (billiard_search.cpp:1358-1405 per node) -------------------------------------
+            std::vector<std::shared_ptr<Frame>> batchFrames;
+            std::unordered_map<const Frame*, int> slotOf;
+            std::vector<int32_t> stateIdx;
+            int slots = 0;
+            for (auto& node : batch) {
+                auto frame = frameOf(breakRoot(node.get()));
+                auto it = slotOf.find(frame.get());
+                if (it == slotOf.end()) {
+                    it = slotOf.insert({frame.get(), (int)batchFrames.size()}).first;
+                    batchFrames.push_back(frame);
+                    slots = std::max(slots, (int)frame->state._balls.size());
+                }
+                stateIdx.push_back(it->second);
+            }
+            if (slots > BCU_MAX_BALLS) throw std::runtime_error("billiard::search::cuda: more than 32 balls");
+            const size_t nF = batchFrames.size(), m = batch.size();
+            std::vector<float> pos(nF * slots * 2, 0.0f);
+            std::vector<int32_t> types(nF * slots, -1);
+            std::vector<uint32_t> mask(nF, 0u);
+            for (size_t f = 0; f < nF; ++f) {
+                const Frame& frame = *batchFrames[f];
+                for (size_t b = 0; b < frame.state._balls.size(); ++b) {
+                    pos[(f * slots + b) * 2] = frame.state._balls[b]._position.x;
+                    pos[(f * slots + b) * 2 + 1] = frame.state._balls[b]._position.y;
+                    types[f * slots + b] = rules.code(frame.state._balls[b]._type);
+                }
+                for (auto& t : frame.searched) { const int c = rules.code(t); if (c >= 0) mask[f] |= 1u << c; }
+            }
+            std::vector<float> vx(m), vy(m), ftime(m), fpos(m * slots * 2);
+            std::vector<uint64_t> sc(m), bc(m), cost(m);
+            std::vector<uint32_t> flags(m), potted(m);
+            for (size_t i = 0; i < m; ++i) {
+                // the strike is the BALL_SHOT node of the input layer the planner made (prepareForSimulation :797-826)
+                for (auto& kv : batch[i]->asSimulation()->_simulation.firstLayer()._nodes)
+                    if (kv.second._type == node::NodeType::BALL_SHOT) { vx[i] = kv.second.after()->_velocity.x; vy[i] = kv.second.after()->_velocity.y; }
+                sc[i] = batch[i]->_searchCost;
+                bc[i] = batch[i]->_cost;
+            }
+            bcu_engine* e = engine.handle();
+            engine.checked(bcu_set_states(e, (int32_t)nF, slots, pos.data(), types.data(), mask.data(), nullptr), "bcu_set_states");
+            bcu_results out{cost.data(), flags.data(), potted.data(), ftime.data(), fpos.data(), nullptr};
+            engine.checked(bcu_evaluate(e, (int64_t)m, stateIdx.data(), vx.data(), vy.data(), sc.data(), bc.data(), &out), "bcu_evaluate");
+            report.simulations += m;
+            report.batches++;
+            // ---- results, node by node (:1388-1462) --------------------------------------------------------------------------
+            for (size_t i = 0; i < m; ++i) {
+                if (!(flags[i] & BCU_F_COMPLETED) || !(flags[i] & BCU_F_VALID)) continue;   // discarded / "End state is not valid"
+                auto& node = batch[i];
+                const Frame& frame = *batchFrames[stateIdx[i]];
+                node->asSimulation()->_cost = (double)(cost[i] - node->_cost);   // simCost (:1403-1405)
+                int simCount = 0;
+                for (const SearchNode* p = node.get(); p; p = p->_parent.get()) simCount += p->_type == SearchNodeType::SIMULATION;
+                bool solution = true;
+                if (config._depthSearchEnabled && simCount < _options.breaks) {
+                    std::vector<Ball> rest;   // the balls at rest in the final layer, with the types of the frame (:1410-1426)
+                    std::unordered_map<std::string, std::string> idsByType;
+                    for (size_t b = 0; b < frame.state._balls.size(); ++b) {
+                        const Ball& ball = frame.state._balls[b];
+                        if (!((potted[i] >> b) & 1u))
+                            rest.emplace_back(glm::vec2{fpos[(i * slots + b) * 2], fpos[(i * slots + b) * 2 + 1]}, ball._type, ball._id);
+                        if (!idsByType.count(ball._type)) idsByType.insert({ball._type, ball._id});
+                    }
+                    State nextState{rest};
+                    Search nextSearch = config._rules._nextSearch(nextState, frame.searched);
+                    State modified = config._rules._modifyState(nextState, idsByType);
+                    if (modified._balls.empty()) continue;   // "could not replace all balls!" (:1432-1435)
+                    bool hasTypeToSearch = false;
+                    for (auto& ball : modified._balls)
+                        if ((hasTypeToSearch = std::count(nextSearch._types.begin(), nextSearch._types.end(), ball._type) > 0)) break;
+                    if (hasTypeToSearch) {
+                        solution = false;
+                        for (auto& root : addPocketsAsInitialTargets(modified, nextSearch, config)) {
+                            root->_parent = node;
+                            root->_cost = cost[i];
+                            root->_searchCost = 0;
+                            open.push(Open{root, order++});
+                        }
+                    }
+                }
+                if (solution) {
+                    node->_isSolution = true;
+                    node->_cost = cost[i];
+                    solutions.push_back(Open{node, order++});
+                }
+            }
+            if (cancelled()) { report.cancelled = true; return result; }
+            if (elapsedMs() >= (double)_options.maxDurationMs) { report.noTimeLeft = true; break; }
+        }
+
+        // ---- mapToSolution (:185-222): one node::System per break of every solution, ascending ------------------------------
+        std::sort(solutions.begin(), solutions.end(), [](const Open& a, const Open& b) {
+            return a.node->_cost != b.node->_cost ? a.node->_cost < b.node->_cost : a.order < b.order;
+        });
+        report.solutions = solutions.size();
+        for (auto& s : solutions) report.costs.push_back(s.node->_cost);
+        if (!solutions.empty()) {
+            // all strikes of all solutions are traced in one device call; a SIMULATION node shared by several solutions once
+            std::vector<SearchNode*> simNodes;
+            std::unordered_map<SearchNode*, int> seen;
+            for (auto& s : solutions)
+                for (SearchNode* p = s.node.get(); p; p = p->_parent.get())
+                    if (p->_type == SearchNodeType::SIMULATION && !seen.count(p)) { seen.insert({p, (int)simNodes.size()}); simNodes.push_back(p); }
+            std::vector<std::shared_ptr<Frame>> traceFrames;
+            std::unordered_map<const Frame*, int> slotOf;
+            std::vector<int32_t> stateIdx;
+            int slots = 0;
+            for (SearchNode* p : simNodes) {
+                auto frame = frameOf(breakRoot(p));
+                auto it = slotOf.find(frame.get());
+                if (it == slotOf.end()) {
+                    it = slotOf.insert({frame.get(), (int)traceFrames.size()}).first;
+                    traceFrames.push_back(frame);
+                    slots = std::max(slots, (int)frame->state._balls.size());
+                }
+                stateIdx.push_back(it->second);
+            }
+            const size_t nF = traceFrames.size();
+            std::vector<float> pos(nF * slots * 2, 0.0f);
+            std::vector<int32_t> types(nF * slots, -1);
+            std::vector<uint32_t> mask(nF, 0xffffffffu);
+            for (size_t f = 0; f < nF; ++f)
+                for (size_t b = 0; b < traceFrames[f]->state._balls.size(); ++b) {
+                    pos[(f * slots + b) * 2] = traceFrames[f]->state._balls[b]._position.x;
+                    pos[(f * slots + b) * 2 + 1] = traceFrames[f]->state._balls[b]._position.y;
+                    types[f * slots + b] = rules.code(traceFrames[f]->state._balls[b]._type);
+                }
+            bcu_engine* e = engine.handle();
+            engine.checked(bcu_set_states(e, (int32_t)nF, slots, pos.data(), types.data(), mask.data(), nullptr), "bcu_set_states");
+            const size_t recPer = (size_t)BCU_MAX_LAYERS * slots * BCU_TRACE_REC;
+            for (size_t first = 0; first < simNodes.size(); first += 4096) {   // bcu_trace_strikes takes up to 65 536; 4096 bounds the host buffers
+                const size_t m = std::min<size_t>(4096, simNodes.size() - first);
+                std::vector<float> vx(m), vy(m), times(m * BCU_MAX_LAYERS), rec(m * recPer);
+                std::vector<int32_t> layers(m);
+                for (size_t i = 0; i < m; ++i)
+                    for (auto& kv : simNodes[first + i]->asSimulation()->_simulation.firstLayer()._nodes)
+                        if (kv.second._type == node::NodeType::BALL_SHOT) { vx[i] = kv.second.after()->_velocity.x; vy[i] = kv.second.after()->_velocity.y; }
+                engine.checked(bcu_trace_strikes(e, (int32_t)m, stateIdx.data() + first, vx.data(), vy.data(), layers.data(), times.data(),
+                                                 rec.data()), "bcu_trace_strikes");
+                for (size_t i = 0; i < m; ++i) {
+                    auto system = engine.systemFromTrace(traceFrames[stateIdx[first + i]]->state, layers[i], &times[i * BCU_MAX_LAYERS],
+                                                         &rec[i * recPer], slots);
+                    if (!system) throw std::runtime_error("billiard::search::cuda: a solution's strike did not re-simulate");
+                    auto simulation = simNodes[first + i]->asSimulation();
+                    system->_id = simulation->_simulation._id;
+                    simulation->_simulation = std::move(*system);
+                }
+            }
+            for (auto& s : solutions) result.push_back(s.node->allSimulations());   // type.hpp:525-537
+        }
+        report.ms = elapsedMs();
+        return result;
+    }
+
+    SearchOptions _options;
+    std::mutex _lock;
+    std::condition_variable _wake;
+    std::unique_ptr<Request> _pending;
+    bool _cancel = false, _exit = false;
+    SearchReport _report;
+    std::unique_ptr<Engine> _engine;
+    std::vector<float> _engineKey;
+    std::thread _worker;   // last: started when everything above exists
+};
+
+// == billiard::search::search(state, search, solutions, config), billiard_search.hpp:9-12.  Like the reference's, the
+// manager behind it is a function-local static that lives until the process exits (billiard_search.cpp:86-90).
+inline std::future<std::vector<std::vector<node::System>>> search(const State& state, const Search& search, uint16_t solutions,
+                                                                   const Configuration& config) {
+    static SearchFront front{};
+    return front.process(state, search, solutions, config);
+}
 
 }  // namespace billiard::search::cuda

@@ -18,6 +18,14 @@ class _SnookerConfig(C.Structure):
                 ("minimum", C.c_float * 2), ("maximum", C.c_float * 2)]
 
 
+class BreakRulesDesc(C.Structure):
+    """bcu_break_rules (include/billiard_cuda.h): the rules between breaks as data for bcu_search_levels."""
+    _fields_ = [("kind", C.c_int32), ("snooker", _SnookerConfig)]
+
+
+BREAK_RULES_SINGLE, BREAK_RULES_REPEAT, BREAK_RULES_SNOOKER = 0, 1, 2
+
+
 def _p(a, t):
     return a.ctypes.data_as(C.POINTER(t))
 
@@ -48,6 +56,12 @@ class SnookerRules:
         c.maximum[0], c.maximum[1] = np.float32(maximum[0]), np.float32(maximum[1])
         self.cfg = c
         self.spots = np.array([[c.spots[k][0], c.spots[k][1]] for k in range(6)], np.float32)
+
+    def descriptor(self):
+        d = BreakRulesDesc()
+        d.kind = BREAK_RULES_SNOOKER
+        d.snooker = self.cfg
+        return d
 
     def next_search(self, types, present, previous_types):
         """-> list of type codes the next break searches for (-1 = the reference's empty type name)."""
@@ -83,12 +97,36 @@ class SnookerRules:
 class RepeatRules:
     """Not in the reference (it ships snooker rules only; Configuration's default rules end the search after one break,
     type.hpp:324-332): the next break searches for the same types again and the state is left as it is.  Used for the
-    pool layouts of BASELINE configs (rules as a plug-in)."""
+    pool layouts of BASELINE configs (rules as a plug-in).  The search itself runs the C++ restatement
+    (BCU_BREAK_RULES_REPEAT in csrc/bcu_search.cpp); the methods below are the host-side statement of the same rule."""
 
     name = "repeat"
 
+    def descriptor(self):
+        d = BreakRulesDesc()
+        d.kind = BREAK_RULES_REPEAT
+        return d
+
     def next_search(self, types, present, previous_types):
         return list(previous_types)
+
+    def state_after_break(self, pos, types, present):
+        return True, np.array(pos, np.float32, copy=True), np.array(present, np.uint8, copy=True)
+
+
+class SingleBreakRules:
+    """The reference Configuration's default rules (type.hpp:325-328): nextSearch returns an empty Search, so every valid
+    strike is a solution after one break; the state is left as it is."""
+
+    name = "single"
+
+    def descriptor(self):
+        d = BreakRulesDesc()
+        d.kind = BREAK_RULES_SINGLE
+        return d
+
+    def next_search(self, types, present, previous_types):
+        return []
 
     def state_after_break(self, pos, types, present):
         return True, np.array(pos, np.float32, copy=True), np.array(present, np.uint8, copy=True)

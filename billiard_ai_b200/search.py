@@ -1,93 +1,103 @@
-"""Level-synchronous multi-break search on top of the engine (BASELINE configs 3 and 4).
-
-The reference searches break after break best-first (billiard_search.cpp:74-98, expand :1358-1471): a finished, valid
-simulation either is a solution or -- when depth search is on and fewer than BREAKS simulations lie on its path -- seeds
-the next break: the balls at rest form the next State, `_rules._nextSearch` names the types to pot next and
-`_rules._modifyState` puts potted colours back (:1407-1462).  Here the same step is taken for a whole beam at once:
+"""Multi-break search on top of the engine (BASELINE configs 3 and 4): a ctypes binding of bcu_search_levels
+(include/billiard_cuda.h; csrc/bcu_search.cpp), the level-synchronous restatement of the reference's best-first search over
+breaks (billiard_search.cpp:74-98, expand :224-244, next-break seeding :1407-1462):
 
     level L:  beam states x (directions x speeds)  --engine-->  cost = state's accumulated cost + simulationCost,
               validity against the state's expected types      --device top-k on (cost, id), merged across GPUs-->
-              the k best strikes with their end states         --rules (host, rules.py)-->  level L + 1 states / solutions
+              the k best strikes with their end states         --rules, one C++ pass over the k records-->
+              level L + 1 states / solutions
 
-Every rank runs this loop; the candidate ids of a level are sharded by contiguous range and the per-rank beams are merged
-by the engine's one collective (bcu_level_select), after which all ranks hold the identical beam and apply the rules
-identically -- no other exchange.
+The whole loop runs inside the library (C++); nothing here touches a candidate.  Every rank calls it with the same
+arguments; the candidate ids of a level are sharded by contiguous range over the ranks of the engine's communicator and
+the per-rank beams are merged by the engine's one collective, after which all ranks hold the identical beam and apply the
+rules identically -- no other exchange.
 """
+import ctypes as C
+
 import numpy as np
 
-from .workloads import GRID_SEARCH_COST, shard_range
+from .rules import BreakRulesDesc
+from .workloads import GRID_SEARCH_COST
 
 
-def _mask_of(type_codes):
-    m = 0
-    for t in type_codes:
-        if t >= 0:
-            m |= 1 << int(t)
-    return m
+class _SearchParams(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("beam", C.c_int32), ("n_dirs", C.c_int32), ("n_speeds", C.c_int32),
+                ("dirs", C.POINTER(C.c_float)), ("speeds", C.POINTER(C.c_float)), ("search_cost", C.c_uint64),
+                ("n_search_types", C.c_int32), ("search_types", C.POINTER(C.c_int32)), ("min_solutions", C.c_int32),
+                ("max_duration_ms", C.c_uint32), ("cancel", C.POINTER(C.c_int32))]
+
+
+class _LevelStats(C.Structure):
+    _fields_ = [("states", C.c_int32), ("beam", C.c_int32), ("candidates", C.c_int64), ("kernel_ms", C.c_float),
+                ("rules_ms", C.c_float), ("wall_ms", C.c_float)]
+
+
+class _SearchResult(C.Structure):
+    _fields_ = [("capacity", C.c_int32), ("count", C.c_int32), ("total", C.c_int32), ("levels_run", C.c_int32),
+                ("stopped", C.c_int32), ("wall_ms", C.c_float), ("cost", C.POINTER(C.c_uint64)), ("breaks", C.POINTER(C.c_int32)),
+                ("dir_index", C.POINTER(C.c_int32)), ("speed_index", C.POINTER(C.c_int32)), ("strike", C.POINTER(C.c_float)),
+                ("frame_pos", C.POINTER(C.c_float)), ("frame_types", C.POINTER(C.c_int32)), ("end_pos", C.POINTER(C.c_float)),
+                ("end_present", C.POINTER(C.c_uint8)), ("stats", C.POINTER(_LevelStats))]
+
+
+STOPPED = {0: "exhausted", 1: "enough_solutions", 2: "timeout", 3: "cancelled"}
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
 
 
 def search_levels(engine, pos, types, search_types, levels, beam, dirs, speeds, rules, search_cost=GRID_SEARCH_COST,
-                  rank=0, world=1, stats=None):
+                  rank=None, world=None, stats=None, min_solutions=0, max_duration_ms=0, cancel=None, info=None):
     """-> solutions, ascending by (cost, discovery order): dicts with `cost`, `strikes` (one (vx, vy) per break),
     `dirs` / `speeds` (grid indices per break), `frames` (the (pos, types) frame each break was played on), `pos` /
     `present` (table after the last break, rules applied when a further break was seeded) and `breaks`.
 
     pos, types: the frame (types < 0: no ball in that slot).  search_types: type codes the first break may pot.
-    `stats`, if given, receives per-level dicts (states, candidates, beam entries, ms of device time)."""
+    rules: SnookerRules / RepeatRules / SingleBreakRules (rules.py) -- handed to the library as a bcu_break_rules descriptor.
+    `stats`, if given, receives per-level dicts (states, candidates, beam entries, ms of device / rules / wall time);
+    `info` (a dict) receives `stopped`, `total`, `levels_run`, `wall_ms`.  rank / world are those of the engine's
+    communicator (bcu_comm_init); the arguments are only checked against it.
+    min_solutions / max_duration_ms / cancel (a ctypes c_int32 another thread may set): the three ways the reference's
+    manager ends a search (process.hpp:188-198), looked at between levels."""
     pos = np.ascontiguousarray(pos, np.float32)
     types = np.ascontiguousarray(types, np.int32)
-    n_dirs, n_speeds = len(dirs), len(speeds)
-    per_state = n_dirs * n_speeds
     dirs = np.ascontiguousarray(dirs, np.float32)
     speeds = np.ascontiguousarray(speeds, np.float32)
-    states = [dict(pos=pos, types=types, searched=[int(t) for t in search_types], cost=0, path=[])]
-    solutions = []
-    for level in range(levels):
-        if not states:
-            break
-        s_pos = np.stack([s["pos"] for s in states])
-        s_types = np.stack([s["types"] for s in states])
-        s_mask = np.array([_mask_of(s["searched"]) for s in states], np.uint32)
-        s_cost = np.array([s["cost"] for s in states], np.uint64)
-        engine.set_states(s_pos, s_types, s_mask, base_cost=s_cost)
-        total = len(states) * per_state
-        lo, hi = shard_range(total, rank, world)
-        engine.evaluate_grid(dirs, speeds, search_cost, first=lo, count=hi - lo)
-        ms = engine.last_kernel_ms() if stats is not None else 0.0
-        engine.level_select(beam)
-        b = engine.fetch_beam()
-        if stats is not None:
-            stats.append(dict(level=level, states=len(states), candidates=total, beam=len(b["cost"]), kernel_ms=ms))
-        nxt = []
-        for cost, cid, potted, fpos in zip(b["cost"].tolist(), b["id"].tolist(), b["potted"].tolist(), b["final_pos"]):
-            si, rem = divmod(int(cid), per_state)
-            k, j = divmod(rem, n_speeds)
-            parent = states[si]
-            vx = np.float32(speeds[j] * dirs[k, 0]); vy = np.float32(speeds[j] * dirs[k, 1])
-            path = parent["path"] + [(k, j, float(vx), float(vy), parent["pos"], parent["types"])]
-            frame_types = parent["types"]
-            present = ((frame_types >= 0) & (((potted >> np.arange(len(frame_types))) & 1) == 0)).astype(np.uint8)
-            rest_pos = np.where(present[:, None].astype(bool), fpos, 0.0).astype(np.float32)
-            sol = dict(cost=int(cost), breaks=level + 1, strikes=[(p[2], p[3]) for p in path], dirs=[p[0] for p in path],
-                       speeds=[p[1] for p in path], frames=[(p[4], p[5]) for p in path], pos=rest_pos, present=present)
-            if level + 1 >= levels:                                         # simCount == BREAKS (:1407)
-                solutions.append(sol)
-                continue
-            search = rules.next_search(frame_types, present, parent["searched"])
-            ok, pos2, present2 = rules.state_after_break(rest_pos, frame_types, present)
-            if not ok:                                                       # "could not replace all balls" (:1432-1435)
-                continue
-            on = present2.astype(bool)
-            if any(on[i] and int(frame_types[i]) in search for i in range(len(frame_types))):   # hasTypeToSearch (:1437-1443)
-                nxt.append(dict(pos=np.where(on[:, None], pos2, 0.0).astype(np.float32),
-                                types=np.where(on, frame_types, -1).astype(np.int32), searched=search, cost=int(cost),
-                                path=path))
-            else:
-                sol["pos"], sol["present"] = pos2, present2
-                solutions.append(sol)
-        states = nxt
-    solutions.sort(key=lambda s: s["cost"])   # stable: equal costs stay in discovery order
-    return solutions
+    st = np.ascontiguousarray(search_types, np.int32)
+    nb, cap = len(types), int(levels) * int(beam)
+    if rank is not None or world is not None:
+        er, ew = engine.rank_info()
+        assert (rank is None or rank == er) and (world is None or world == ew), "rank / world differ from the engine's communicator"
+    desc = rules if isinstance(rules, BreakRulesDesc) else rules.descriptor()
+    sp = _SearchParams(int(levels), int(beam), len(dirs), len(speeds), _p(dirs, C.c_float), _p(speeds, C.c_float),
+                       int(search_cost), len(st), _p(st, C.c_int32), int(min_solutions), int(max_duration_ms),
+                       C.pointer(cancel) if cancel is not None else C.POINTER(C.c_int32)())
+    cost = np.zeros(cap, np.uint64); breaks = np.zeros(cap, np.int32)
+    di = np.zeros((cap, levels), np.int32); si = np.zeros((cap, levels), np.int32)
+    strike = np.zeros((cap, levels, 2), np.float32)
+    fpos = np.zeros((cap, levels, nb, 2), np.float32); ftypes = np.zeros((cap, levels, nb), np.int32)
+    epos = np.zeros((cap, nb, 2), np.float32); epresent = np.zeros((cap, nb), np.uint8)
+    lst = (_LevelStats * int(levels))()
+    res = _SearchResult(cap, 0, 0, 0, 0, 0.0, _p(cost, C.c_uint64), _p(breaks, C.c_int32), _p(di, C.c_int32), _p(si, C.c_int32),
+                        _p(strike, C.c_float), _p(fpos, C.c_float), _p(ftypes, C.c_int32), _p(epos, C.c_float),
+                        _p(epresent, C.c_uint8), lst)
+    engine._ck(engine.lib.bcu_search_levels(engine.h, C.c_int32(nb), _p(pos, C.c_float), _p(types, C.c_int32), C.byref(sp),
+                                            C.byref(desc), C.byref(res)), "bcu_search_levels")
+    if stats is not None:
+        for lv in range(res.levels_run):
+            s = lst[lv]
+            stats.append(dict(level=lv, states=s.states, candidates=s.candidates, beam=s.beam, kernel_ms=s.kernel_ms,
+                              rules_ms=s.rules_ms, wall_ms=s.wall_ms))
+    if info is not None:
+        info.update(stopped=STOPPED.get(res.stopped, res.stopped), total=res.total, levels_run=res.levels_run, wall_ms=res.wall_ms)
+    out = []
+    for r in range(res.count):
+        b = int(breaks[r])
+        out.append(dict(cost=int(cost[r]), breaks=b, strikes=[(float(strike[r, l, 0]), float(strike[r, l, 1])) for l in range(b)],
+                        dirs=di[r, :b].tolist(), speeds=si[r, :b].tolist(), frames=[(fpos[r, l], ftypes[r, l]) for l in range(b)],
+                        pos=epos[r], present=epresent[r]))
+    return out
 
 
 def solution_traces(engine, solutions, top=None):
@@ -101,7 +111,7 @@ def solution_traces(engine, solutions, top=None):
     frames, slot, sidx, vx, vy = [], {}, [], [], []
     for s in sols:
         for (fpos, ftypes), (svx, svy) in zip(s["frames"], s["strikes"]):
-            key = id(fpos)
+            key = (fpos.tobytes(), ftypes.tobytes())
             if key not in slot:
                 slot[key] = len(frames)
                 frames.append((fpos, ftypes))

@@ -199,6 +199,73 @@ int bcu_snooker_next_search(const bcu_snooker_config* cfg, int32_t n_balls, cons
 int bcu_snooker_state_after_break(const bcu_snooker_config* cfg, int32_t n_balls, const float* pos, const int32_t* types,
                                   const uint8_t* present, float* out_pos, uint8_t* out_present, int32_t* out_ok);
 
+/* ---- the multi-break search as one call (billiard::search::search, billiard_search.hpp:9-12) -----------------------
+ * Level-synchronous restatement of the reference's best-first search over breaks (billiard_search.cpp:74-98, 224-244,
+ * next-break seeding :1407-1462): per level every beam state x (n_dirs x n_speeds) grid strike is simulated, the `beam`
+ * best valid strikes are selected on the device (merged across the ranks of bcu_comm_init: every rank calls this function
+ * with the same arguments and evaluates its contiguous share of the candidate ids), and ONE host pass over the selected
+ * records applies the rules between breaks: empty state => dropped, no ball of a searched type left => solution, else a
+ * state of the next level.  Strikes of the last level (simCount == BREAKS) are solutions. */
+#define BCU_MAX_SEARCH_LEVELS 8
+/* The rules between breaks (Configuration::_rules._nextSearch / _modifyState, type.hpp:324-332) as data: */
+#define BCU_BREAK_RULES_SINGLE 0   /* the Configuration's defaults: nextSearch = Search{} (nothing left to search: every valid
+                                      strike is a solution after one break), modifyState = identity (type.hpp:325-328) */
+#define BCU_BREAK_RULES_REPEAT 1   /* not in the reference (it ships snooker rules only): search the same types again, state as
+                                      it is -- the pool layouts of BASELINE configs 1 and 3 */
+#define BCU_BREAK_RULES_SNOOKER 2  /* billiard::snooker::nextSearch / stateAfterBreak (billiard_snooker.cpp:792-822, 1097-1126) */
+typedef struct bcu_break_rules {
+    int32_t kind;
+    bcu_snooker_config snooker;    /* kind BCU_BREAK_RULES_SNOOKER */
+} bcu_break_rules;
+typedef struct bcu_search_params {
+    int32_t levels;                /* BREAKS (billiard_search.cpp:15), 1..BCU_MAX_SEARCH_LEVELS */
+    int32_t beam;                  /* strikes kept per level, 1..1024 */
+    int32_t n_dirs, n_speeds;      /* the candidate grid of every state (as bcu_evaluate_grid) */
+    const float* dirs;             /* [n_dirs][2] */
+    const float* speeds;           /* [n_speeds] */
+    uint64_t search_cost;          /* SearchNode::_searchCost of every strike */
+    int32_t n_search_types;        /* Search::_types of the first break */
+    const int32_t* search_types;
+    /* the manager's three ways to end a search (process.hpp:188-198), looked at between levels: */
+    int32_t min_solutions;         /* > 0: stop once this many solutions are final (`solutions` of search()); 0: all levels */
+    uint32_t max_duration_ms;      /* > 0: wall-clock budget (the reference: 10 000 ms); 0: none */
+    const volatile int32_t* cancel;/* may be NULL; set non-zero by another thread to abandon the search (a newer request,
+                                      process.hpp:82-83, 261-268) */
+} bcu_search_params;
+typedef struct bcu_level_stats {
+    int32_t states, beam;          /* beam states evaluated, strikes selected */
+    int64_t candidates;            /* strikes of the level, all ranks */
+    float kernel_ms;               /* the level's simulation launch on this rank (CUDA events) */
+    float rules_ms, wall_ms;       /* host pass over the beam; the whole level */
+} bcu_level_stats;
+#define BCU_SEARCH_EXHAUSTED 0     /* all levels run / no state left */
+#define BCU_SEARCH_ENOUGH 1        /* min_solutions reached */
+#define BCU_SEARCH_TIMEOUT 2
+#define BCU_SEARCH_CANCELLED 3
+typedef struct bcu_search_result {
+    int32_t capacity;              /* in: room for this many solutions in the arrays below */
+    int32_t count;                 /* out: solutions written, ascending by cost (equal costs in discovery order) */
+    int32_t total;                 /* out: solutions found */
+    int32_t levels_run;            /* out */
+    int32_t stopped;               /* out: BCU_SEARCH_* */
+    float wall_ms;                 /* out: the whole call */
+    uint64_t* cost;                /* [capacity] accumulated cost of the solution */
+    int32_t* breaks;               /* [capacity] strikes on its path */
+    /* any of the following may be NULL; per break b < breaks (entries past `breaks` are -1 / 0): */
+    int32_t* dir_index;            /* [capacity][levels] */
+    int32_t* speed_index;          /* [capacity][levels] */
+    float* strike;                 /* [capacity][levels][2] the strike's velocity */
+    float* frame_pos;              /* [capacity][levels][n_balls][2] the table the strike was played on ... */
+    int32_t* frame_types;          /* [capacity][levels][n_balls] ... and its types (-1 = no ball): bcu_trace_strikes input */
+    float* end_pos;                /* [capacity][n_balls][2] table after the last break (rules applied when they ended the path) */
+    uint8_t* end_present;          /* [capacity][n_balls] */
+    bcu_level_stats* stats;        /* [levels], may be NULL */
+} bcu_search_result;
+int bcu_search_levels(bcu_engine* e, int32_t n_balls, const float* pos, const int32_t* types, const bcu_search_params* params,
+                      const bcu_break_rules* rules, bcu_search_result* out);
+/* rank / number of ranks of the engine's communicator (0 / 1 without bcu_comm_init) */
+int bcu_engine_rank_info(const bcu_engine* e, int32_t* out_rank, int32_t* out_ranks);
+
 /* ---- measurement hooks -------------------------------------------------------------------------------- */
 /* CUDA-event timer on the engine's stream (the stream every kernel of this library is launched on) */
 int bcu_timer_begin(bcu_engine* e);

@@ -38,15 +38,21 @@ def main(path, counters_path, note):
             v /= 1e3
         elif r[ui] == "ms":
             v *= 1e3
+        elif r[ui] in ("Kbyte", "Mbyte", "Gbyte"):
+            v *= {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[r[ui]]
         launches.setdefault(int(r[0]), dict(kernel=name))[SHORT.get(r[mi], r[mi])] = v
     seq = list(launches.values())
     ends = [i for i, l in enumerate(seq) if l["kernel"] == "pack_records_kernel"]
     starts = [i for i, l in enumerate(seq) if l["kernel"] == "init_kernel"]
     flush = [i for i, l in enumerate(seq) if l["kernel"] == "flush_kernel"]
     end = max(e for e in ends if not flush or e < flush[-1])          # the warm level (no flush in front)
-    start = max(s for s in starts if s < end)
-    # a level runs as 2 parts on 2 streams: both parts' init kernels precede the rounds
-    while start > 0 and seq[start - 1]["kernel"] == "init_kernel":
+    # a level runs as several parts on concurrent streams; under ncu they are serialised part after part (init ... finish,
+    # init ... finish, selection): the level starts where the run of pipeline kernels in front of the selection starts
+    pipe = {"init_kernel", "items_kernel", "quartic_kernel", "apply_kernel", "finish_kernel", "counters_kernel"}
+    start = end
+    while start > 0 and not seq[start - 1]["kernel"] in pipe:
+        start -= 1
+    while start > 0 and seq[start - 1]["kernel"] in pipe:
         start -= 1
     level = seq[start:end + 1]
     per = collections.OrderedDict()
