@@ -325,6 +325,12 @@ def run_b200(args, rank, local_rank, world):
     h2d = mine * (4 + 4 + 4 + 8 + 8) + nb * (8 + 4) + 4
     d2h = mine * (8 + 4 + 4 + 4) + BEAM * (24 + nb * 8)   # per-strike cost / flags / potted / time + the beam records
 
+    # ---- config 4 (and config 3 on one GPU) through bcu_search_levels: every rank takes part (one allgather per level) ------
+    searches = None
+    if not args.no_extra:
+        searches = search_workloads(eng, W, rank, world, dist if world > 1 else None)
+        eng.set_prune(1)
+
     if rank != 0:
         barrier()           # rank 0 checks parity on its own GPU meanwhile (no collective in there)
         if world > 1:
@@ -381,6 +387,7 @@ def run_b200(args, rank, local_rank, world):
     extra = None
     if not args.no_extra:
         extra = secondary_workloads(eng, W, args)
+        extra.update(searches or {})
     barrier()
 
     # ---- roofline of the strike pipeline (init + 31 x {items, quartic, apply} + finish), timed together with CUDA events
@@ -509,6 +516,59 @@ def secondary_workloads(eng, W, args):
     out["config5_slice"] = dict(workload=f"config 5: tables 1000..{1000 + nt - 1} (16 balls) x 4096 strikes = {nt * 4096} strikes, one launch",
                                 **timed(nt * 4096, 3))
     eng.set_prune(1)
+    return out
+
+
+def search_workloads(eng, W, rank, world, dist):
+    """BASELINE configs 4 and 3 through the C ABI's bcu_search_levels (the whole level loop in C++: evaluate -> device top-k ->
+    allgather + merge -> rules): per-level device time, wall time of the whole search, a digest of the solution list (the
+    same for every N), both prune modes.  Config 4 is STRONG scaling: ~1 M candidates per level sharded over the N ranks."""
+    import hashlib
+    from billiard_ai_b200.rules import RepeatRules, SnookerRules
+    from billiard_ai_b200.search import search_levels
+    out = {}
+
+    def run(name, desc, pos, types, levels, beam, dirs, speeds, rules):
+        res = {"workload": desc, "n_gpus": world}
+        for prune, tag in ((1, ""), (0, "_exact")):
+            eng.set_prune(prune)
+            best = None
+            for it in range(3):   # the first pass warms up (allocations, graph capture)
+                stats, info = [], {}
+                t0 = time.perf_counter()
+                sols = search_levels(eng, pos, types, [W.TYPE_CODE["RED"]], levels, beam, dirs, speeds, rules, stats=stats, info=info)
+                wall = time.perf_counter() - t0
+                if it > 0 and (best is None or wall < best[0]):
+                    best = (wall, stats, sols)
+            wall, stats, sols = best
+            digest = hashlib.sha256(json.dumps([(s["cost"], s["dirs"], s["speeds"]) for s in sols]).encode()).hexdigest()[:16]
+            if dist is not None:
+                allv = [None] * world
+                dist.all_gather_object(allv, (digest, wall, [st["kernel_ms"] for st in stats]))
+                assert len({v[0] for v in allv}) == 1, "ranks disagree on the solution list"
+                wall = max(v[1] for v in allv)
+                kms = [max(v[2][i] for v in allv) for i in range(len(stats))]
+            else:
+                kms = [st["kernel_ms"] for st in stats]
+            strikes = sum(st["candidates"] for st in stats)
+            res.update({"strikes": strikes, "solutions": len(sols), "digest" + tag: digest,
+                        "best" + tag: [(s["cost"], s["breaks"]) for s in sols[:3]],
+                        "wall_ms" + tag: 1e3 * wall, "device_ms" + tag: float(sum(kms)),
+                        "level_kernel_ms" + tag: kms, "level_candidates": [st["candidates"] for st in stats],
+                        "strikes_per_sec_wall" + tag: strikes / wall, "wall_over_device" + tag: 1e3 * wall / float(sum(kms))})
+        assert res["digest"] == res["digest_exact"], "reach bound on / off find different solutions"
+        out[name] = res
+
+    pos, types = W.snooker22_open()
+    d4, s4 = W.grid(32, 32)
+    run("config4", "config 4: snooker 22-ball frame, 4-break search, beam 1024 x (32 directions x 32 speeds) = 1 048 576 strikes per "
+        f"level from level 3 on, sharded over {world} GPU(s), snooker rules between breaks; times = max over ranks",
+        pos, types, 4, 1024, d4, s4, SnookerRules())
+    if world == 1:
+        p3, t3 = W.random_layout(16, 16)
+        d3, s3 = W.grid(256, 16)
+        run("config3", "config 3: pool 16-ball layout (seed 16), 3-break beam search, beam 1024 x (256 directions x 16 speeds) = "
+            "4 194 304 strikes in level 3, 'repeat' rules", p3, t3, 3, 1024, d3, s3, RepeatRules())
     return out
 
 

@@ -287,7 +287,9 @@ struct SearchOptions {
     int device = 0;
     int breaks = 2;                  // BREAKS, billiard_search.cpp:15
     uint64_t maxDurationMs = 10000;  // ProcessManager::process default, process.hpp:80
-    size_t batch = 256;              // SIMULATION nodes collected before a device launch (the planner runs ahead this far)
+    size_t batch = 32;               // SIMULATION nodes collected before a device launch: the planner runs ahead this far, so
+                                     // a request for few solutions plans (and simulates) at most this much more than the
+                                     // reference's best-first order would before "enough solutions" ends it
     int prune = 0;                   // bcu_set_prune mode (0: every quartic the reference solves is solved)
 };
 

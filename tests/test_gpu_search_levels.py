@@ -71,14 +71,25 @@ def _oracle_levels(port, ref_rules, pos, types, search_types, levels, beam, dirs
     return solutions, near_tie
 
 
-def _compare(got, want):
-    assert len(got) == len(want) and len(got) > 0
-    for g, w in zip(got, want):
-        assert g["cost"] == w["cost"]
-        assert list(zip(g["dirs"], g["speeds"])) == w["path"]
-        assert np.array_equal(g["present"], w["present"])
-        on = g["present"].astype(bool)
-        assert np.array_equal(g["pos"][on].view(np.uint32), w["pos"][on].view(np.uint32))
+def _same(g, w):
+    on = g["present"].astype(bool)
+    return (g["cost"] == w["cost"] and list(zip(g["dirs"], g["speeds"])) == w["path"] and np.array_equal(g["present"], w["present"])
+            and np.array_equal(g["pos"][on].view(np.uint32), w["pos"][on].view(np.uint32)))
+
+
+def _compare(got, want, near_tie=False):
+    """Every solution must agree: cost, the strike of every break, the end state bit for bit.  A search in which a selected
+    strike has two events within 1e-9 s (north_star's tie clause) is compared all the same -- the engine reproduces the
+    reference's evaluation order, so ties resolve identically in practice; only if such a search differs is the comparison
+    cut at the first differing solution, and everything in front of it must still agree."""
+    assert len(got) > 0
+    first_bad = next((i for i, (g, w) in enumerate(zip(got, want)) if not _same(g, w)), None)
+    if first_bad is None:
+        assert len(got) == len(want)
+        return
+    assert near_tie, f"solution {first_bad} differs and no selected strike is near a tie"
+    assert first_bad > 0, "a near tie changed the best solution"
+    pytest.skip(f"near tie: solutions agree up to entry {first_bad} of {len(want)}")
 
 
 @pytest.mark.parametrize("seed", [22, 5])
@@ -95,9 +106,7 @@ def test_snooker_three_break_search_matches_the_oracle_loop(engine, port, seed):
     stats = []
     got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 24, dirs, speeds, rules, stats=stats)
     want, near_tie = _oracle_levels(port, ref_rules, pos, types, [W.TYPE_CODE["RED"]], 3, 24, dirs, speeds, W.GRID_SEARCH_COST)
-    if near_tie:
-        pytest.skip("a selected strike has two events within 1e-9 s (north_star tie clause)")
-    _compare(got, want)
+    _compare(got, want, near_tie)
     assert max(s["breaks"] for s in got) == 3 and len(stats) == 3
     assert any(len(set(np.nonzero(s["present"])[0])) < 22 for s in got)
 
@@ -113,10 +122,67 @@ def test_pool_three_break_beam_search_matches_the_oracle_loop(engine, port):
     got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 32, dirs, speeds, RepeatRules())
     want, near_tie = _oracle_levels(port, None, pos, types, [W.TYPE_CODE["RED"]], 3, 32, dirs, speeds, W.GRID_SEARCH_COST,
                                     repeat=True)
-    if near_tie:
-        pytest.skip("a selected strike has two events within 1e-9 s (north_star tie clause)")
-    _compare(got, want)
+    _compare(got, want, near_tie)
     assert got[0]["breaks"] == 3
+
+
+def test_config4_shape_at_beam_256_matches_the_oracle_loop(engine, port):
+    """Config 4 closer to its real size (what the host cores do in under a minute): 22-ball snooker frame, 3 breaks, beam 256,
+    64 x 16 strikes per state (262 144 strikes per level after the first), the reference's own rules between the breaks."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import SnookerRules
+    from billiard_ai_b200.search import search_levels
+    rules = SnookerRules()
+    pos, types = W.snooker22_open(22)
+    dirs, speeds = W.grid(64, 16)
+    info = {}
+    got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 256, dirs, speeds, rules, info=info)
+    want, near_tie = _oracle_levels(port, RefRules(rules), pos, types, [W.TYPE_CODE["RED"]], 3, 256, dirs, speeds, W.GRID_SEARCH_COST)
+    _compare(got, want, near_tie)
+    assert info["stopped"] == "exhausted" and info["levels_run"] == 3 and info["total"] == len(want)
+
+
+def test_config3_shape_at_beam_256_matches_the_oracle_loop(engine, port):
+    """Config 3 closer to its real size: 16-ball pool frame, 3 breaks, beam 256, 64 x 16 strikes per state, 'repeat' rules."""
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import RepeatRules
+    from billiard_ai_b200.search import search_levels
+    pos, types = W.random_layout(16, 16)
+    dirs, speeds = W.grid(64, 16)
+    got = search_levels(engine, pos, types, [W.TYPE_CODE["RED"]], 3, 256, dirs, speeds, RepeatRules())
+    want, near_tie = _oracle_levels(port, None, pos, types, [W.TYPE_CODE["RED"]], 3, 256, dirs, speeds, W.GRID_SEARCH_COST, repeat=True)
+    _compare(got, want, near_tie)
+
+
+def test_search_levels_ends_like_the_manager(engine):
+    """process.hpp:188-198: enough solutions / time budget / a newer request end a search between levels; the single-break
+    rule set (the Configuration's defaults) makes every valid strike a solution after one break."""
+    import ctypes as C
+    from billiard_ai_b200 import workloads as W
+    from billiard_ai_b200.rules import RepeatRules, SingleBreakRules, SnookerRules
+    from billiard_ai_b200.search import search_levels
+    pos, types = W.snooker22_open(22)
+    dirs, speeds = W.grid(48, 6)
+    red = [W.TYPE_CODE["RED"]]
+    info = {}
+    one = search_levels(engine, pos, types, red, 3, 24, dirs, speeds, SingleBreakRules(), info=info)
+    assert len(one) == 24 and all(s["breaks"] == 1 for s in one) and info["levels_run"] == 1
+    costs = [s["cost"] for s in one]
+    assert costs == sorted(costs)
+    full = search_levels(engine, pos, types, red, 3, 24, dirs, speeds, SnookerRules())
+    assert full and all(s["breaks"] >= 2 for s in full)   # depth search: a first-break strike alone is not a solution here
+    cancel = C.c_int32(1)
+    info = {}
+    none = search_levels(engine, pos, types, red, 3, 24, dirs, speeds, RepeatRules(), cancel=cancel, info=info)
+    assert none == [] and info["stopped"] == "cancelled" and info["levels_run"] == 0
+    info = {}
+    few = search_levels(engine, pos, types, red, 8, 24, dirs, speeds, RepeatRules(), max_duration_ms=1, info=info)
+    assert info["stopped"] == "timeout" and info["levels_run"] < 8 and few == []
+    # min_solutions: snooker paths that run out of searched types end early; once enough of them are final the search stops
+    info = {}
+    deep = search_levels(engine, pos, types, red, 3, 24, dirs, speeds, SnookerRules(), min_solutions=1, info=info)
+    assert info["stopped"] in ("exhausted", "enough_solutions")
+    assert len(deep) >= 1 and [s["cost"] for s in deep] == sorted(s["cost"] for s in deep)
 
 
 def test_config3_full_size_properties(engine):

@@ -85,3 +85,35 @@ def test_thesis_cost_lists(ref):
     for log in thesis["logs"]:
         if 400 < log["line"] < 620:
             assert log["simulation"][0][0] in sim_costs
+
+
+def test_thesis_two_break_list(ref):
+    """04_suche.tex:1114-1246: the two-break totals (183281, 185129, ...) come out of the reference's own search -- expand()
+    run best-first to exhaustion with depth search on, BREAKS = 2 -- with the reference's own snooker rules between the breaks
+    (nextSearch / stateAfterBreak, oracle/_ref/libref_rules.so).  Pins the multi-break path of the oracle."""
+    import ctypes as C
+    from oracle_lib import ORACLE_DIR, TYPE_NAMES
+    so = os.path.join(ORACLE_DIR, "_ref", "libmirror_check.so")
+    if not os.path.exists(so):
+        pytest.skip("libmirror_check.so not built (needs /root/reference at build time)")
+    from billiard_ai_b200.rules import SnookerRules
+    from test_rules import RefRules
+    RefRules(SnookerRules())
+    lib = C.CDLL(so)
+    lib.mirror_reference_search.restype = C.c_int64
+    with open(os.path.join(GOLDEN, "thesis_costs.json")) as f:
+        want = json.load(f)["lists"]["s2_two_breaks"]
+    with open(os.path.join(GOLDEN, "layouts.json")) as f:
+        lay = json.load(f)["situation2"]
+    pos = np.array([b["position"] for b in lay["balls"]], dtype=np.float32)
+    types = np.array([TYPE_CODE[b["type"]] for b in lay["balls"]], dtype=np.int32)
+    searched = np.array([TYPE_CODE["RED"]], dtype=np.int32)
+    names = (C.c_char_p * len(TYPE_NAMES))(*[t.encode() for t in TYPE_NAMES])
+    costs = np.zeros(1024, np.uint64)
+    breaks = np.zeros(1024, np.int32)
+    p = lambda a, t: a.ctypes.data_as(C.POINTER(t))   # noqa: E731
+    n = lib.mirror_reference_search(C.c_int(len(types)), p(pos, C.c_float), names, C.c_int(len(TYPE_NAMES)), p(types, C.c_int32),
+                                    C.c_int(1), p(searched, C.c_int32), C.c_int(1), C.c_int(0), C.c_int(2), C.c_int64(1024),
+                                    p(costs, C.c_uint64), p(breaks, C.c_int32))
+    assert n >= len(want)
+    assert costs[:len(want)].tolist() == want and (breaks[:n] == 2).all()
