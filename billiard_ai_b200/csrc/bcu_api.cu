@@ -105,8 +105,10 @@ struct bcu_engine {
     cudaEvent_t pipeFork = nullptr;
     DevBuf<LaunchParams> dPipeParams;   // one parameter block per stream, read by the kernels
     bool useGraph = true;               // BCU_NO_GRAPH / BCU_ROUND_TIMING: plain stream launches
-    cudaGraphExec_t pipeGraph = nullptr;
-    PipeGraphKey pipeKey{};
+    // captured launch sequences, most recently used first: a multi-break search alternates between a few launch shapes
+    // (level sizes), and re-capturing 190 kernel nodes costs more than a small level takes to run
+    static constexpr int PIPE_GRAPH_CACHE = 8;
+    std::vector<std::pair<PipeGraphKey, cudaGraphExec_t>> pipeGraphs;
     // top-k
     DevBuf<unsigned char> dTopkScratch;
     DevBuf<uint64_t> dTopCost, dTopId;
@@ -268,6 +270,9 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
     e->pipeCfg.roundTiming = getenv("BCU_ROUND_TIMING") != nullptr;
     if (const char* pv = getenv("BCU_PDL")) e->pipeCfg.pdlMode = atoi(pv);
+    if (const char* gv = getenv("BCU_GRID_PCT")) { const int v = atoi(gv); e->pipeCfg.gridPct = v < 5 ? 5 : v > 400 ? 400 : v; }
+    if (const char* lv = getenv("BCU_LAYOUT")) e->pipeCfg.layout = atoi(lv) == 0 ? 0 : 1;
+    if (const char* lv = getenv("BCU_STEP_LANES")) e->pipeCfg.stepLanes = atoi(lv);
     e->selectTiming = getenv("BCU_SELECT_TIMING") != nullptr;
     if (const char* jv = getenv("BCU_JOBS_PER_STRIKE")) {   // initial quartic-queue capacity (tests force the overflow path)
         const int v = atoi(jv);
@@ -312,7 +317,7 @@ void bcu_destroy(bcu_engine* e) {
         if (e->pipeStream[g]) cudaStreamDestroy(e->pipeStream[g]);
     }
     if (e->pipeFork) cudaEventDestroy(e->pipeFork);
-    if (e->pipeGraph) cudaGraphExecDestroy(e->pipeGraph);
+    for (auto& kv : e->pipeGraphs) cudaGraphExecDestroy(kv.second);
     e->dPipeParams.release();
     if (e->evT0) cudaEventDestroy(e->evT0);
     if (e->evT1) cudaEventDestroy(e->evT1);
@@ -480,8 +485,17 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
                 }
                 PipeGraphKey key{e->dPipeWs.p, e->dPipeParams.p, per, G, nBalls, e->jobsPerStrike, withCounters, e->pruneMode};
                 const bool useGraph = e->useGraph;
-                if (!useGraph || !e->pipeGraph || !(key == e->pipeKey)) {
-                    if (e->pipeGraph) { cudaGraphExecDestroy(e->pipeGraph); e->pipeGraph = nullptr; }
+                cudaGraphExec_t graphExec = nullptr;
+                for (size_t gi = 0; useGraph && gi < e->pipeGraphs.size(); ++gi) {
+                    if (e->pipeGraphs[gi].first == key) {
+                        auto hit = e->pipeGraphs[gi];
+                        e->pipeGraphs.erase(e->pipeGraphs.begin() + gi);
+                        e->pipeGraphs.insert(e->pipeGraphs.begin(), hit);
+                        graphExec = hit.second;
+                        break;
+                    }
+                }
+                if (!useGraph || !graphExec) {
                     if (useGraph) CK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
                     CK(cudaEventRecord(e->pipeFork, e->stream));
                     for (int g = 0; g < G; ++g) {
@@ -500,13 +514,17 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
                     if (useGraph) {
                         cudaGraph_t graph = nullptr;
                         CK(cudaStreamEndCapture(e->stream, &graph));
-                        CK(cudaGraphInstantiate(&e->pipeGraph, graph, 0));
+                        CK(cudaGraphInstantiate(&graphExec, graph, 0));
                         cudaGraphDestroy(graph);
-                        e->pipeKey = key;
+                        if ((int)e->pipeGraphs.size() >= bcu_engine::PIPE_GRAPH_CACHE) {
+                            cudaGraphExecDestroy(e->pipeGraphs.back().second);
+                            e->pipeGraphs.pop_back();
+                        }
+                        e->pipeGraphs.insert(e->pipeGraphs.begin(), {key, graphExec});
                     }
                 }
-                if (useGraph) CK(cudaGraphLaunch(e->pipeGraph, e->stream));
-                e->launches += (int64_t)G * pipeline_launch_count();
+                if (useGraph) CK(cudaGraphLaunch(graphExec, e->stream));
+                e->launches += (int64_t)G * pipeline_launch_count(e->pipeCfg);
                 CK(cudaEventRecord(e->evStop, e->stream));
                 bool onCopyStream = false;
                 if (out && nParts <= G) {

@@ -85,6 +85,7 @@ struct PipeWorkspace {
     uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner; bit 31 = audit mark
     int pdlEarly;              // kernels signal cudaTriggerProgrammaticLaunchCompletion() at once (launch_pipeline)
     int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
+    int fused;                 // layout of a round: 1 = step + quartic (bcu_step.cuh; one key / T buffer), 0 = items + quartic + apply
 };
 // Per-engine launch configuration of the pipeline (no process-wide state: two engines on two devices or threads each
 // own one).  Filled by bcu_create from the BCU_* environment; the occupancy figures are computed on first use for the
@@ -92,6 +93,11 @@ struct PipeWorkspace {
 struct PipeLaunchCfg {
     int occItems = 0, occQuartic = 0, occApply = 0;
     size_t occSmem = ~(size_t)0;
+    int occStep = 0;
+    int layout = 0;            // BCU_LAYOUT: 0 = the three-kernel round (default), 1 = fused step kernel (bcu_step.cuh: bit-exact,
+                               // measured 3-4 x slower: groups of lanes per strike leave most lanes idle)
+    int stepLanes = 8;         // BCU_STEP_LANES: lanes of a warp that own one strike in step_kernel (4, 8 or 16)
+    int gridPct = 100;         // BCU_GRID_PCT (experiment): grids of the round kernels as a percentage of one resident wave
     int pdlMode = 1;           // BCU_PDL: 0 off, 1 programmatic dependent launch, 2 + early trigger
     bool roundTiming = false;  // BCU_ROUND_TIMING (diagnosis): CUDA events around every kernel, times on stderr
 };
@@ -100,7 +106,7 @@ const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
 void pipeline_upload_constants(cudaStream_t stream);
 cudaError_t launch_pipeline(const LaunchParams* dParams, int nBalls, int nRails, int nPockets, bool withCounters,
                             const PipeWorkspace& w, int sms, cudaStream_t stream, bool resetOverflow, PipeLaunchCfg& cfg);
-int pipeline_launch_count();
+int pipeline_launch_count(const PipeLaunchCfg& cfg);
 
 void upload_constants(cudaStream_t stream);   // physics constants only (identical for every engine)
 cudaError_t launch_trace(const LaunchParams& p, cudaStream_t stream);

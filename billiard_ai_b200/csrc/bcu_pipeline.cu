@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb) {
     const uint32_t posted = w.counts[4 * round + 2];
     const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
-    unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
+    unsigned long long* key = w.key + (w.fused ? (size_t)0 : (size_t)(round % 3) * w.n);
     for (uint64_t j = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)nb * QUARTIC_BLOCK) {
         float co[5];
         #pragma unroll
@@ -306,12 +306,11 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
     uint32_t* liveCountNext = &w.counts[4 * (round + 1) + 0];
     uint32_t* dynCountNext = &w.counts[4 * (round + 1) + 1];
     const bool overflow = round + 1 > MAX_EVENTS;  // billiard_search.cpp:1376-1379 (every live strike has `round` events)
-    const int64_t stride = (int64_t)nb * BS;
-
     // ---- the event of every live strike (createLayer :1957-1992) ----------------------------------------------------
     // One pass over both lists: tile i of the live strikes and tile i of the dynamic balls are handled by the same CTA
     // iteration (they touch different balls), so their memory round trips overlap and one list reservation serves both.
     const int64_t nMax = nLive > nDyn ? (int64_t)nLive : (int64_t)nDyn;
+    const int64_t stride = (int64_t)nb * BS;
     for (int64_t base = (int64_t)bid * BS; base < nMax; base += stride) {
         const int64_t idx = base + threadIdx.x;
         bool appendLive = false, appendA = false, appendB = false;
@@ -445,6 +444,8 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
     apply_body(ash, *pp, w, round, blockIdx.x, gridDim.x);
 }
 
+#include "bcu_step.cuh"
+
 // rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
 // One warp per strike, lane = ball.
 __device__ __forceinline__ void finish_body(const LaunchParams& p, const PipeWorkspace& w, unsigned bid, unsigned nb) {
@@ -563,7 +564,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     return off;
 }
 
-int pipeline_launch_count() { return 2 + 3 * ROUNDS; }
+int pipeline_launch_count(const PipeLaunchCfg& cfg) { return cfg.layout == 1 ? 2 + (ROUNDS + 1) + ROUNDS : 2 + 3 * ROUNDS; }
 
 // One launch of the batch path over p->nCand <= w.n strikes.  `p` is a DEVICE pointer (the kernels read their parameters
 // from memory, so a captured CUDA graph of this sequence stays valid from call to call); all grids are persistent and
@@ -589,7 +590,13 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // persistent grids: exactly one resident wave of every kernel
     int& occItems = cfg.occItems; int& occQuartic = cfg.occQuartic; int& occApply = cfg.occApply;
     size_t& occSmem = cfg.occSmem;
+    const int lanes = cfg.stepLanes == 4 ? 4 : cfg.stepLanes == 16 ? 16 : 8;
+    const size_t stepSmem = (size_t)(STEP_BLOCK / lanes) * step_group_bytes(nBalls);
+    auto stepKernel = lanes == 4 ? step_kernel<4> : lanes == 16 ? step_kernel<16> : step_kernel<8>;
     if (occSmem != itemSmem) {
+        if (stepSmem > 48 * 1024) cudaFuncSetAttribute(stepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stepSmem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occStep, stepKernel, STEP_BLOCK, stepSmem);
+        if (cfg.occStep < 1) cfg.occStep = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occItems, items_kernel, ITEM_BLOCK, itemSmem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occQuartic, quartic_kernel, QUARTIC_BLOCK, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occApply, apply_kernel, APPLY_BLOCK, 0);
@@ -610,6 +617,8 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     auto cfgOf = [&](unsigned grid, unsigned block, size_t smem) {
         cudaLaunchConfig_t c{};
+        grid = (unsigned)((uint64_t)grid * (uint64_t)cfg.gridPct / 100u);
+        if (grid < 1) grid = 1;
         c.gridDim = dim3(grid); c.blockDim = dim3(block); c.dynamicSmemBytes = smem; c.stream = stream;
         c.attrs = attr; c.numAttrs = pdl ? 1 : 0;
         return c;
@@ -618,7 +627,21 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     mark();
-    for (int r = 0; r < ROUNDS; ++r) {
+    w.fused = cfg.layout == 1;
+    if (w.fused) {
+        // a round is two kernels: step k applies event k of every live strike and collects the candidates of the new layer
+        // (rest / rolling / rail / pocket times -> the strike's key, ball pairs -> quartic jobs); quartic k solves the jobs
+        for (int k = 0; k <= ROUNDS; ++k) {
+            cudaLaunchConfig_t cs = cfgOf(sms * cfg.occStep, STEP_BLOCK, stepSmem);
+            if ((e = cudaLaunchKernelEx(&cs, stepKernel, p, w, k)) != cudaSuccess) return e;
+            mark();
+            if (k == ROUNDS) break;
+            cudaLaunchConfig_t cq = cfgOf(sms * occQuartic, QUARTIC_BLOCK, 0);
+            if ((e = cudaLaunchKernelEx(&cq, quartic_kernel, w, k)) != cudaSuccess) return e;
+            mark();
+        }
+    }
+    for (int r = 0; r < ROUNDS && !w.fused; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * occItems, ITEM_BLOCK, itemSmem);
         if ((e = cudaLaunchKernelEx(&ci, items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
@@ -634,7 +657,23 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if ((e = cudaLaunchKernelEx(&cf, finish_kernel, p, w)) != cudaSuccess) return e;
     }
     mark();
-    if (timing) {
+    if (timing && w.fused) {
+        cudaStreamSynchronize(stream);
+        std::vector<uint32_t> counts(4 * (ROUNDS + 1));
+        cudaMemcpy(counts.data(), w.counts, counts.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+        auto ms = [&](size_t i) { float t = 0; cudaEventElapsedTime(&t, ev[i], ev[i + 1]); return t * 1000.0f; };
+        float sum[2] = {0, 0};
+        fprintf(stderr, "[bcu timing] init %.1f us\n", ms(0));
+        for (int k = 0; k <= ROUNDS; ++k) {
+            const float ts = ms(1 + 2 * k), tq = k < ROUNDS ? ms(2 + 2 * k) : 0.0f;
+            fprintf(stderr, "[bcu timing] step %2d live %7u jobs %7u : step %6.1f quartic %6.1f us\n", k, counts[4 * k],
+                    k < ROUNDS ? counts[4 * k + 2] : 0u, ts, tq);
+            sum[0] += ts; sum[1] += tq;
+        }
+        float tot = 0; cudaEventElapsedTime(&tot, ev.front(), ev.back());
+        fprintf(stderr, "[bcu timing] finish %.1f us; step %.0f quartic %.0f; total %.0f us\n", ms(ev.size() - 2), sum[0], sum[1], tot * 1000.0f);
+        for (auto x : ev) cudaEventDestroy(x);
+    } else if (timing) {
         cudaStreamSynchronize(stream);
         std::vector<uint32_t> counts(4 * (ROUNDS + 1));
         cudaMemcpy(counts.data(), w.counts, counts.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost);
