@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libbilliard_cuda.so")
-SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_api.cu", "bcu_rules.cpp", "bcu_search.cpp"]
+SOURCES = ["bcu_kernels.cu", "bcu_pipeline.cu", "bcu_topk.cu", "bcu_merge.cu", "bcu_plan.cu", "bcu_api.cu", "bcu_rules.cpp", "bcu_search.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",

@@ -14,6 +14,7 @@
 
 #include "../../include/billiard_cuda.h"
 #include "bcu_kernels.cuh"
+#include "bcu_planner.cuh"
 
 using namespace bcu;
 
@@ -130,6 +131,15 @@ struct bcu_engine {
     void* ncclComm = nullptr;
     int nRanks = 1, rank = 0;
     int64_t idBase = 0;  // global id of candidate 0 of the next bcu_evaluate (multi-GPU shards of explicit lists)
+
+    // the reference's planner on the device (bcu_set_planner / bcu_plan)
+    bool havePlanner = false;
+    PlanTable planTable{};
+    DevBuf<PlanTable> dPlanTable;
+    DevBuf<uint32_t> dPlanItemCount, dPlanBlockSum;
+    DevBuf<unsigned long long> dPlanBlockOffset, dPlanTotal;
+    int64_t planCount = -1;          // strikes of the last bcu_plan (in dCandState / dVx / dVy / dSearchCost / dBaseCost)
+    int planStates = 0;              // nStates the plan was made for
 
     LaunchParams last{};
     bool haveLast = false;
@@ -302,6 +312,7 @@ void bcu_destroy(bcu_engine* e) {
     e->dEventLog.release(); e->dTraceTimes.release(); e->dTraceRec.release(); e->dCounters.release(); e->dPipeWs.release();
     e->dTable.release(); e->dRules.release();
     e->dTrPos.release(); e->dTrType.release(); e->dTrExpected.release();
+    e->dPlanTable.release(); e->dPlanItemCount.release(); e->dPlanBlockSum.release(); e->dPlanBlockOffset.release(); e->dPlanTotal.release();
     if (e->hTypeStage) cudaFreeHost(e->hTypeStage);
     if (e->evStage) cudaEventDestroy(e->evStage);
     e->dTopkScratch.release(); e->dTopCost.release(); e->dTopId.release(); e->dTopCount.release();
@@ -378,6 +389,7 @@ int bcu_set_states(bcu_engine* e, int32_t nStates, int32_t nBalls, const float* 
     e->nStates = nStates;
     e->nBalls = nBalls;
     e->haveLast = false;
+    e->planCount = -1;
     return BCU_OK;
 }
 
@@ -604,6 +616,7 @@ static int evaluate_impl(bcu_engine* e, int64_t n, const int32_t* stateIdx, cons
     CK(cudaSetDevice(e->device));
     CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n));
     CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
+    e->planCount = -1;   // the candidate arrays now hold the caller's strikes
     const bool wantPos = out && out->final_pos, wantLog = out && out->event_log;
     // final positions are always produced on the device (the beam records need them); they are copied out on request
     int rc = reserve_results(e, n, true, wantLog);
@@ -734,6 +747,7 @@ int bcu_simulate_trace(bcu_engine* e, int32_t nBalls, const float* pos, const in
     const int32_t s0 = 0;
     const uint64_t sc = 0, bc = 0;
     CK(e->dCandState.reserve(1)); CK(e->dVx.reserve(1)); CK(e->dVy.reserve(1)); CK(e->dSearchCost.reserve(1)); CK(e->dBaseCost.reserve(1));
+    e->planCount = -1;
     rc = reserve_results(e, 1, true, false);
     if (rc) { e->nBalls = savedBalls; return rc; }
     e->haveLast = false;   // the per-strike result arrays now hold the traced strike
@@ -781,6 +795,7 @@ int bcu_trace_strikes(bcu_engine* e, int32_t n, const int32_t* stateIdx, const f
     const int NB = e->nBalls;
     const size_t recPer = (size_t)BCU_MAX_LAYERS * NB * BCU_TRACE_REC;
     CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n)); CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
+    e->planCount = -1;
     int rc = reserve_results(e, n, true, false);
     if (rc) return rc;
     CK(e->dTraceTimes.reserve((size_t)n * BCU_MAX_LAYERS)); CK(e->dTraceRec.reserve((size_t)n * recPer));
@@ -1090,6 +1105,96 @@ int bcu_get_counters(bcu_engine* e, uint64_t* out5) {
 }
 
 int64_t bcu_launch_count(const bcu_engine* e) { return e ? e->launches : 0; }
+
+// ---- the reference's geometric planner on the device (bcu_planner.cuh, bcu_plan.cu) --------------------------------------
+int bcu_set_planner(bcu_engine* e, const bcu_planner_desc* d) {
+    if (!e) return BCU_ERR_INVALID;
+    if (!d || d->n_rails != e->table.nRails || !d->rail_start || (d->n_set_order > 0 && !d->set_order) || d->n_search_pockets < 1 ||
+        !d->search_pockets)
+        return fail(e, BCU_ERR_INVALID, "bcu_set_planner: bad description (the rails must be those of bcu_create)");
+    CK(cudaSetDevice(e->device));
+    PlanTable tb;
+    if (!plan_table_build(&tb, d->n_rails, e->railDerived.data(), d->rail_start, d->rail_order, d->n_set_order, d->set_order,
+                          d->n_search_pockets, d->search_pockets, e->table.diameter / 2, d->minimal_pocket_velocity,
+                          d->diagonal_length_squared, d->velocity_multiply, e->rules.cueType))
+        return fail(e, BCU_ERR_INVALID, "bcu_set_planner: inconsistent rail orders / counts");
+    // (the ball radius: bcu_create keeps diameter = radius * 2, an exact doubling, so diameter / 2 is the radius bit for bit)
+    e->planTable = tb;
+    CK(e->dPlanTable.reserve(1));
+    CK(cudaMemcpyAsync(e->dPlanTable.p, &e->planTable, sizeof(PlanTable), cudaMemcpyHostToDevice, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    e->havePlanner = true;
+    e->planCount = -1;
+    return BCU_OK;
+}
+
+int bcu_plan(bcu_engine* e, int64_t* outCount) {
+    if (!e || !outCount) return BCU_ERR_INVALID;
+    if (!e->havePlanner) return fail(e, BCU_ERR_STATE, "bcu_plan: call bcu_set_planner first");
+    if (e->nStates == 0) return fail(e, BCU_ERR_STATE, "bcu_plan: call bcu_set_states first");
+    CK(cudaSetDevice(e->device));
+    StateTable st{};
+    st.nStates = e->nStates; st.nBalls = e->nBalls;
+    st.pos = e->dStatePos.p; st.type = e->dStateType.p; st.expectedMask = e->dExpected.p;
+    const uint64_t* base = e->hasStateBase ? e->dStateBase.p : nullptr;
+    const int64_t items = plan_work_items(e->planTable, e->nStates, e->nBalls), blocks = plan_blocks(e->planTable, e->nStates, e->nBalls);
+    CK(e->dPlanItemCount.reserve((size_t)(items > 0 ? items : 1))); CK(e->dPlanBlockSum.reserve((size_t)(blocks > 0 ? blocks : 1)));
+    CK(e->dPlanBlockOffset.reserve((size_t)(blocks > 0 ? blocks : 1))); CK(e->dPlanTotal.reserve(1));
+    CK(launch_plan_count(e->dPlanTable.p, e->planTable, st, base, e->dPlanItemCount.p, e->dPlanBlockSum.p, e->dPlanBlockOffset.p,
+                         e->dPlanTotal.p, e->stream));
+    e->launches += 2;
+    unsigned long long total = 0;
+    CK(cudaMemcpyAsync(&total, e->dPlanTotal.p, sizeof(total), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    const size_t n = (size_t)(total > 0 ? total : 1);
+    CK(e->dCandState.reserve(n)); CK(e->dVx.reserve(n)); CK(e->dVy.reserve(n)); CK(e->dSearchCost.reserve(n)); CK(e->dBaseCost.reserve(n));
+    if (total > 0) {
+        CK(launch_plan_write(e->dPlanTable.p, e->planTable, st, base, e->dPlanItemCount.p, e->dPlanBlockOffset.p, e->dCandState.p, e->dVx.p,
+                             e->dVy.p, e->dSearchCost.p, e->dBaseCost.p, e->stream));
+        e->launches += 1;
+    }
+    e->planCount = (int64_t)total;
+    e->planStates = e->nStates;
+    e->haveLast = false;
+    *outCount = (int64_t)total;
+    return BCU_OK;
+}
+
+int bcu_fetch_plan(bcu_engine* e, int64_t offset, int64_t n, int32_t* stateIdx, float* vx, float* vy, uint64_t* searchCost, uint64_t* cost) {
+    if (!e) return BCU_ERR_INVALID;
+    if (e->planCount < 0) return fail(e, BCU_ERR_STATE, "bcu_fetch_plan: no plan (bcu_plan; bcu_set_states / bcu_evaluate discard it)");
+    if (offset < 0 || n < 0 || offset + n > e->planCount) return fail(e, BCU_ERR_INVALID, "bcu_fetch_plan: range");
+    if (n == 0) return BCU_OK;
+    CK(cudaSetDevice(e->device));
+    if (stateIdx) CK(cudaMemcpyAsync(stateIdx, e->dCandState.p + offset, n * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (vx) CK(cudaMemcpyAsync(vx, e->dVx.p + offset, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (vy) CK(cudaMemcpyAsync(vy, e->dVy.p + offset, n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    if (searchCost) CK(cudaMemcpyAsync(searchCost, e->dSearchCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+    if (cost) CK(cudaMemcpyAsync(cost, e->dBaseCost.p + offset, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return BCU_OK;
+}
+
+int bcu_evaluate_plan(bcu_engine* e, const bcu_results* out) {
+    if (!e) return BCU_ERR_INVALID;
+    if (e->planCount < 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate_plan: no plan (bcu_plan; bcu_set_states / bcu_evaluate discard it)");
+    const int64_t n = e->planCount;
+    if (n == 0) return BCU_OK;
+    CK(cudaSetDevice(e->device));
+    const bool wantLog = out && out->event_log;
+    int rc = reserve_results(e, n, true, wantLog);
+    if (rc) return rc;
+    LaunchParams p;
+    fill_common(e, p, n, true, wantLog);
+    p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
+    p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
+    e->last = p; e->haveLast = true; e->lastFirst = 0;
+    bool copied = false;
+    rc = run(e, p, false, out, &copied);
+    if (rc) { e->haveLast = false; return rc; }
+    if (!copied) { rc = copy_back(e, 0, n, out); if (rc) return rc; }
+    return BCU_OK;
+}
 
 int bcu_engine_rank_info(const bcu_engine* e, int32_t* outRank, int32_t* outRanks) {
     if (!e) return BCU_ERR_INVALID;

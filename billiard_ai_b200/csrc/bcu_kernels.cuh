@@ -123,6 +123,16 @@ cudaError_t launch_pack_records(const uint64_t* keyCost, const uint64_t* keyId, 
                                 const uint32_t* potted, const float* finalTime, const float* finalPos, int nBalls,
                                 void* out, cudaStream_t stream);
 cudaError_t launch_merge_records(const void* gathered, int G, int k, int nBalls, void* out, cudaStream_t stream);
+// the reference's planner on the device; see bcu_plan.cu / bcu_planner.cuh
+struct PlanTable;
+int64_t plan_work_items(const PlanTable& tb, int nStates, int nBalls);
+int64_t plan_blocks(const PlanTable& tb, int nStates, int nBalls);
+cudaError_t launch_plan_count(const PlanTable* dTable, const PlanTable& hTable, const StateTable& states, const uint64_t* stateBase,
+                              uint32_t* itemCount, uint32_t* blockSum, unsigned long long* blockOffset, unsigned long long* total,
+                              cudaStream_t stream);
+cudaError_t launch_plan_write(const PlanTable* dTable, const PlanTable& hTable, const StateTable& states, const uint64_t* stateBase,
+                              const uint32_t* itemCount, const unsigned long long* blockOffset, int32_t* stateIdx, float* vx, float* vy,
+                              uint64_t* searchCost, uint64_t* cost, cudaStream_t stream);
 // measurement helpers
 int launch_issue_rate(int kind, int ctas, int iters, double* sink, cudaStream_t stream);
 cudaError_t launch_flush(void* buf, size_t bytes, cudaStream_t stream);

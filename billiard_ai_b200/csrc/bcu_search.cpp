@@ -62,7 +62,7 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
                                  const bcu_search_params* sp, const bcu_break_rules* rules, bcu_search_result* out) {
     if (!e || !pos || !types || !sp || !rules || !out) return BCU_ERR_INVALID;
     if (nBalls < 1 || nBalls > BCU_MAX_BALLS || sp->levels < 1 || sp->levels > BCU_MAX_SEARCH_LEVELS || sp->beam < 1 || sp->beam > 1024 ||
-        sp->n_dirs < 1 || sp->n_speeds < 1 || !sp->dirs || !sp->speeds || sp->n_search_types < 0 ||
+        sp->n_dirs < 0 || (sp->n_dirs > 0 && (sp->n_speeds < 1 || !sp->dirs || !sp->speeds)) || sp->n_search_types < 0 ||
         (sp->n_search_types > 0 && !sp->search_types) || out->capacity < 0 ||
         (out->capacity > 0 && (!out->cost || !out->breaks)) ||
         (rules->kind != BCU_BREAK_RULES_SINGLE && rules->kind != BCU_BREAK_RULES_REPEAT && rules->kind != BCU_BREAK_RULES_SNOOKER))
@@ -71,7 +71,13 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
     int32_t rank = 0, world = 1;
     bcu_engine_rank_info(e, &rank, &world);
     const int NB = nBalls, L = sp->levels, K = sp->beam;
-    const int64_t perState = (int64_t)sp->n_dirs * sp->n_speeds;
+    // candidates of a state: the direction x speed grid, or -- n_dirs == 0 -- the strikes the reference's planner finds for it
+    // (bcu_set_planner; planned and simulated on the device, one rank)
+    const bool planned = sp->n_dirs == 0;
+    if (planned && world > 1) return BCU_ERR_INVALID;
+    const int64_t perState = planned ? 0 : (int64_t)sp->n_dirs * sp->n_speeds;
+    std::vector<int32_t> planState;
+    std::vector<float> planVx, planVy;
 
     std::vector<std::vector<BeamState>> levels(1);
     {
@@ -82,6 +88,7 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
         levels[0].push_back(std::move(root));
     }
     std::vector<Found> found;
+    std::vector<std::pair<float, float>> planVel;   // velocities of the selected planned strikes, all levels
     std::vector<float> sPos, bTime, bPos;
     std::vector<int32_t> sTypes;
     std::vector<uint32_t> sMask, bPotted;
@@ -109,18 +116,30 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
         int rc = bcu_set_states(e, nS, NB, sPos.data(), sTypes.data(), sMask.data(), sCost.data());
         if (rc) return rc;
         // this rank's contiguous share of the level's candidate ids; the merged beam is identical on every rank
-        const int64_t total = (int64_t)nS * perState;
-        const int64_t per = (total + world - 1) / world;
-        const int64_t lo = std::min(total, (int64_t)rank * per), hi = std::min(total, lo + per);
-        rc = bcu_evaluate_grid(e, sp->n_dirs, sp->n_speeds, sp->dirs, sp->speeds, sp->search_cost, lo, hi - lo);
-        if (rc) return rc;
+        int64_t total = (int64_t)nS * perState;
+        if (planned) {
+            rc = bcu_plan(e, &total);
+            if (rc) return rc;
+            planState.resize((size_t)total); planVx.resize((size_t)total); planVy.resize((size_t)total);
+            rc = bcu_fetch_plan(e, 0, total, planState.data(), planVx.data(), planVy.data(), nullptr, nullptr);
+            if (rc) return rc;
+            rc = total > 0 ? bcu_evaluate_plan(e, nullptr) : BCU_OK;
+            if (rc) return rc;
+        } else {
+            const int64_t per = (total + world - 1) / world;
+            const int64_t lo = std::min(total, (int64_t)rank * per), hi = std::min(total, lo + per);
+            rc = bcu_evaluate_grid(e, sp->n_dirs, sp->n_speeds, sp->dirs, sp->speeds, sp->search_cost, lo, hi - lo);
+            if (rc) return rc;
+        }
         float kernelMs = 0.0f;
-        if (out->stats) bcu_last_kernel_ms(e, &kernelMs);
-        rc = bcu_level_select(e, K);
-        if (rc) return rc;
         int32_t nBeam = 0;
-        rc = bcu_fetch_beam(e, &nBeam, bCost.data(), bId.data(), bPotted.data(), bTime.data(), bPos.data());
-        if (rc) return rc;
+        if (!planned || total > 0) {
+            if (out->stats) bcu_last_kernel_ms(e, &kernelMs);
+            rc = bcu_level_select(e, K);
+            if (rc) return rc;
+            rc = bcu_fetch_beam(e, &nBeam, bCost.data(), bId.data(), bPotted.data(), bTime.data(), bPos.data());
+            if (rc) return rc;
+        }
         const auto tRules = std::chrono::steady_clock::now();
 
         std::vector<BeamState> next;
@@ -128,9 +147,15 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
         std::vector<float> rest((size_t)NB * 2), pos2((size_t)NB * 2);
         for (int b = 0; b < nBeam; ++b) {
             const int64_t cid = (int64_t)bId[b];
-            const int si = (int)(cid / perState);
-            const int64_t rem = cid - (int64_t)si * perState;
-            const int k = (int)(rem / sp->n_speeds), j = (int)(rem - (int64_t)k * sp->n_speeds);
+            int si, k, j;   // planned strikes: k = index into this level's plan (its velocity is kept below), j = -1
+            if (planned) {
+                si = planState[(size_t)cid]; k = (int)planVel.size(); j = -1;
+                planVel.push_back({planVx[(size_t)cid], planVy[(size_t)cid]});
+            } else {
+                si = (int)(cid / perState);
+                const int64_t rem = cid - (int64_t)si * perState;
+                k = (int)(rem / sp->n_speeds); j = (int)(rem - (int64_t)k * sp->n_speeds);
+            }
             const BeamState& parent = states[si];
             // the balls at rest in the final layer form the next State (:1411-1426)
             for (int i = 0; i < NB; ++i) {
@@ -217,9 +242,12 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
         int si = f.state, k = f.dir, j = f.speed;
         for (int l = f.breaks - 1; l >= 0; --l) {
             const BeamState& s = levels[l][si];
-            if (out->dir_index) out->dir_index[(size_t)r * L + l] = k;
-            if (out->speed_index) out->speed_index[(size_t)r * L + l] = j;
-            if (out->strike) {   // as the kernel decodes a grid candidate: one binary32 multiply per component
+            if (out->dir_index) out->dir_index[(size_t)r * L + l] = planned ? -1 : k;
+            if (out->speed_index) out->speed_index[(size_t)r * L + l] = planned ? -1 : j;
+            if (out->strike && planned) {
+                out->strike[((size_t)r * L + l) * 2] = planVel[(size_t)k].first;
+                out->strike[((size_t)r * L + l) * 2 + 1] = planVel[(size_t)k].second;
+            } else if (out->strike) {   // as the kernel decodes a grid candidate: one binary32 multiply per component
                 out->strike[((size_t)r * L + l) * 2] = sp->speeds[j] * sp->dirs[2 * k];
                 out->strike[((size_t)r * L + l) * 2 + 1] = sp->speeds[j] * sp->dirs[2 * k + 1];
             }

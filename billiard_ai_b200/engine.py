@@ -38,6 +38,13 @@ class _RulesDesc(C.Structure):
     _fields_ = [("n_types", C.c_int32), ("cue_type", C.c_int32), ("score", C.POINTER(C.c_double))]
 
 
+class _PlannerDesc(C.Structure):
+    _fields_ = [("n_rails", C.c_int32), ("rail_start", C.POINTER(C.c_float)), ("rail_order", C.POINTER(C.c_int32)),
+                ("n_set_order", C.c_int32), ("set_order", C.POINTER(C.c_int32)), ("n_search_pockets", C.c_int32),
+                ("search_pockets", C.POINTER(C.c_float)), ("minimal_pocket_velocity", C.c_float),
+                ("diagonal_length_squared", C.c_float), ("velocity_multiply", C.c_int32)]
+
+
 class _Results(C.Structure):
     _fields_ = [("cost", C.POINTER(C.c_uint64)), ("flags", C.POINTER(C.c_uint32)), ("potted", C.POINTER(C.c_uint32)),
                 ("final_time", C.POINTER(C.c_float)), ("final_pos", C.POINTER(C.c_float)),
@@ -68,6 +75,11 @@ def load_library(path=None):
     lib.bcu_host_free.argtypes = [C.c_void_p]
     lib.bcu_get_prune.argtypes = [C.c_void_p]
     lib.bcu_test_merge_records.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.bcu_set_planner.argtypes = [C.c_void_p, C.c_void_p]
+    lib.bcu_plan.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    lib.bcu_fetch_plan.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                   C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.bcu_evaluate_plan.argtypes = [C.c_void_p, C.c_void_p]
     lib.bcu_engine_rank_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.bcu_search_levels.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p,
                                       C.c_void_p]
@@ -433,6 +445,48 @@ class Engine:
 
     def launch_count(self):
         return int(self.lib.bcu_launch_count(self.h))
+
+    # ---- the reference's geometric planner on the device (include/billiard_cuda.h: bcu_set_planner ... bcu_evaluate_plan) ----
+    def set_planner(self, tbl, velocity_multiply=True):
+        """tbl: dict in the layout of tests/golden/table.json, the table this engine was created with (same rail order);
+        needs its `railMapOrder` / `railSetOrder` (the reference's container iteration orders) and the pockets' potting points."""
+        ids = [r["id"] for r in tbl["rails"]]
+        self._plan_start = np.ascontiguousarray([[r["start"][0], r["start"][1]] for r in tbl["rails"]], np.float32)
+        self._plan_order = np.ascontiguousarray([ids.index(i) for i in tbl["railMapOrder"]], np.int32)
+        self._plan_set = np.ascontiguousarray([ids.index(i) for i in tbl["railSetOrder"]], np.int32)
+        self._plan_pockets = np.ascontiguousarray([[p["pottingPoint"][0], p["pottingPoint"][1], p["normal"][0], p["normal"][1]]
+                                                   for p in tbl["pockets"]], np.float32)
+        length, width = np.float32(tbl["innerTableLength"]), np.float32(tbl["innerTableWidth"])
+        diag = np.float32(np.float32(length * length) + np.float32(width * width))   # util.cpp:73, binary32
+        d = _PlannerDesc(len(ids), _p(self._plan_start, C.c_float), _p(self._plan_order, C.c_int32), len(self._plan_set),
+                         _p(self._plan_set, C.c_int32), len(self._plan_pockets), _p(self._plan_pockets, C.c_float),
+                         C.c_float(np.float32(tbl["minimalPocketVelocity"])), C.c_float(diag), int(bool(velocity_multiply)))
+        self._ck(self.lib.bcu_set_planner(self.h, C.byref(d)), "bcu_set_planner")
+
+    def plan(self):
+        """Plans every state of the last set_states on the device -> number of strikes planned."""
+        n = C.c_int64(0)
+        self._ck(self.lib.bcu_plan(self.h, C.byref(n)), "bcu_plan")
+        self._plan_n = n.value
+        return n.value
+
+    def fetch_plan(self):
+        n = self._plan_n
+        out = dict(state=np.zeros(n, np.int32), vx=np.zeros(n, np.float32), vy=np.zeros(n, np.float32),
+                   search_cost=np.zeros(n, np.uint64), cost=np.zeros(n, np.uint64))
+        if n:
+            self._ck(self.lib.bcu_fetch_plan(self.h, 0, n, _p(out["state"], C.c_int32), _p(out["vx"], C.c_float), _p(out["vy"], C.c_float),
+                                             _p(out["search_cost"], C.c_uint64), _p(out["cost"], C.c_uint64)), "bcu_fetch_plan")
+        return out
+
+    def evaluate_plan(self, final_pos=True, event_log=False):
+        """Simulates the planned strikes (as evaluate() on them)."""
+        n = self._plan_n
+        out, res = self._result_buffers(n, final_pos, event_log)
+        if n:
+            self._ck(self.lib.bcu_evaluate_plan(self.h, C.byref(res)), "bcu_evaluate_plan")
+        self._last_n = n
+        return self._finish(out)
 
     def rank_info(self):
         """(rank, number of ranks) of the engine's communicator."""

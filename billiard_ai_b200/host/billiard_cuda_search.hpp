@@ -44,6 +44,7 @@
 #include <string>
 #include <thread>
 #include <unordered_map>
+#include <unordered_set>
 #include <utility>
 #include <vector>
 
@@ -268,6 +269,58 @@ private:
     bcu_engine* _e = nullptr;
     RulesTable _rules;
     std::vector<std::string> _railIds, _pocketIds;
+};
+
+}  // namespace billiard::search::cuda
+
+// ---- tables of the device planner (bcu_set_planner) from a Configuration ------------------------------------------------
+namespace billiard::search::cuda {
+
+// The POD arrays behind bcu_planner_desc.  Rails are in the iteration order of Configuration::_table._rails -- the order
+// Engine's constructor hands them to bcu_create -- so rail_order is the identity; set_order is read off a real
+// std::unordered_set<std::string> filled exactly as railCombinations fills its own (billiard_search.cpp:871-880), so it is
+// the reference's order on this standard library.
+struct PlannerTables {
+    std::vector<float> railStart, searchPockets;
+    std::vector<int32_t> setOrder;
+    bcu_planner_desc desc{};
+
+    static PlannerTables from(const Configuration& config) {
+        PlannerTables t;
+        std::unordered_map<std::string, int32_t> indexOf;
+        std::unordered_set<std::string> railIds;
+        for (auto& kv : config._table._rails) {
+            const Rail& r = kv.second;
+            indexOf.insert({kv.first, (int32_t)indexOf.size()});
+            t.railStart.push_back(r._start.x); t.railStart.push_back(r._start.y);
+            if (r._normal.x != 0.0f && r._normal.y != 0.0f) continue;   // ignoreRailInSearch (:860-863)
+            railIds.insert(kv.first);
+        }
+        for (auto& id : railIds) t.setOrder.push_back(indexOf.at(id));
+        for (auto& p : config._searchPockets)
+            t.searchPockets.insert(t.searchPockets.end(), {p._pottingPoint.x, p._pottingPoint.y, p._normal.x, p._normal.y});
+        t.fill(config);
+        return t;
+    }
+    void fill(const Configuration& config) {
+        desc.n_rails = (int32_t)(railStart.size() / 2);
+        desc.rail_start = railStart.data();
+        desc.rail_order = nullptr;
+        desc.n_set_order = (int32_t)setOrder.size();
+        desc.set_order = setOrder.data();
+        desc.n_search_pockets = (int32_t)(searchPockets.size() / 4);
+        desc.search_pockets = searchPockets.data();
+        desc.minimal_pocket_velocity = config._table.minimalPocketVelocity;
+        desc.diagonal_length_squared = config._table.diagonalLengthSquared;
+        desc.velocity_multiply = config._velocityMultiplyEnabled ? 1 : 0;
+    }
+    PlannerTables() = default;
+    PlannerTables(const PlannerTables&) = delete;             // desc points into the vectors
+    PlannerTables& operator=(const PlannerTables&) = delete;
+    PlannerTables(PlannerTables&& o) noexcept : railStart(std::move(o.railStart)), searchPockets(std::move(o.searchPockets)),
+                                                setOrder(std::move(o.setOrder)), desc(o.desc) {
+        desc.rail_start = railStart.data(); desc.set_order = setOrder.data(); desc.search_pockets = searchPockets.data();
+    }
 };
 
 }  // namespace billiard::search::cuda

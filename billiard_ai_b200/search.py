@@ -62,8 +62,9 @@ def search_levels(engine, pos, types, search_types, levels, beam, dirs, speeds, 
     manager ends a search (process.hpp:188-198), looked at between levels."""
     pos = np.ascontiguousarray(pos, np.float32)
     types = np.ascontiguousarray(types, np.int32)
-    dirs = np.ascontiguousarray(dirs, np.float32)
-    speeds = np.ascontiguousarray(speeds, np.float32)
+    planned = dirs is None   # the candidates of a state are the strikes the reference's planner finds (engine.set_planner)
+    dirs = np.ascontiguousarray(dirs if not planned else np.zeros((0, 2)), np.float32)
+    speeds = np.ascontiguousarray(speeds if not planned else np.zeros(0), np.float32)
     st = np.ascontiguousarray(search_types, np.int32)
     nb, cap = len(types), int(levels) * int(beam)
     if rank is not None or world is not None:

@@ -220,7 +220,9 @@ typedef struct bcu_break_rules {
 typedef struct bcu_search_params {
     int32_t levels;                /* BREAKS (billiard_search.cpp:15), 1..BCU_MAX_SEARCH_LEVELS */
     int32_t beam;                  /* strikes kept per level, 1..1024 */
-    int32_t n_dirs, n_speeds;      /* the candidate grid of every state (as bcu_evaluate_grid) */
+    int32_t n_dirs, n_speeds;      /* the candidate grid of every state (as bcu_evaluate_grid); n_dirs = 0: the strikes the
+                                      reference's planner finds for the state instead (bcu_set_planner first; planned and
+                                      simulated on the device; one rank; dir_index / speed_index of the result are -1) */
     const float* dirs;             /* [n_dirs][2] */
     const float* speeds;           /* [n_speeds] */
     uint64_t search_cost;          /* SearchNode::_searchCost of every strike */
@@ -265,6 +267,41 @@ int bcu_search_levels(bcu_engine* e, int32_t n_balls, const float* pos, const in
                       const bcu_break_rules* rules, bcu_search_result* out);
 /* rank / number of ranks of the engine's communicator (0 / 1 without bcu_comm_init) */
 int bcu_engine_rank_info(const bcu_engine* e, int32_t* out_rank, int32_t* out_ranks);
+
+/* ---- the reference's geometric planner on the device --------------------------------------------------
+ * Which strikes are worth simulating on a table state: the reference's best-first expansion of SEARCH nodes -- pocket ->
+ * ball to pot -> ball that hits it -> ... -> cue ball, every link direct or over up to three cushions (billiard_search.cpp:
+ * 299-1347: expandSearchNode*, railCombinations / railTargets, searchCost, calculateMinimalVelocity, prepareForSimulation) --
+ * as an exhaustive enumeration on the device, one thread per (state, pocket, first ball, first link).  It emits exactly the
+ * SIMULATION nodes the reference's expand() creates when run to exhaustion (the same velocities bit for bit, the same
+ * _searchCost and accumulated _cost), for every state of the last bcu_set_states at once: the states' expected_mask is the
+ * Search::_types of the break, their base_cost the cost of the pocket roots.  The planned strikes stay on the device and are
+ * simulated by bcu_evaluate_plan like explicit candidates (ids = position in the plan: ascending by state, then by pocket,
+ * first ball, first link -- deterministic).
+ * Two iteration orders the reference leaves to its hash containers are inputs: rail_order and set_order (below); the C++
+ * mirror reads them off the real containers (billiard_ai_b200/host/billiard_cuda_search.hpp: PlannerTables). */
+typedef struct bcu_planner_desc {
+    int32_t n_rails;               /* the rails of bcu_table_desc, same order */
+    const float* rail_start;       /* [n_rails][2] Rail::_start (unshifted; canReflect, billiard_search.cpp:854-861) */
+    const int32_t* rail_order;     /* [n_rails] or NULL (= as given): iteration order of Configuration::_table._rails
+                                      (railTargets takes the first rail hit in this order, :958-978) */
+    int32_t n_set_order;           /* rails that take part in the search (horizontal / vertical ones, :860-863) */
+    const int32_t* set_order;      /* [n_set_order] iteration order of railCombinations' std::unordered_set of rail ids (:871-897) */
+    int32_t n_search_pockets;      /* Configuration::_searchPockets */
+    const float* search_pockets;   /* [n_search_pockets][4] _pottingPoint.xy, _normal.xy */
+    float minimal_pocket_velocity; /* Configuration::_table.minimalPocketVelocity */
+    float diagonal_length_squared; /* Configuration::_table.diagonalLengthSquared */
+    int32_t velocity_multiply;     /* Configuration::_velocityMultiplyEnabled: also the two faster strikes of a path (:809) */
+} bcu_planner_desc;
+int bcu_set_planner(bcu_engine* e, const bcu_planner_desc* desc);
+/* plans every state of the last bcu_set_states; *out_count = strikes planned (all states) */
+int bcu_plan(bcu_engine* e, int64_t* out_count);
+/* the plan, device -> host: any array may be NULL; cost = SearchNode::_cost of the SIMULATION node (the state's base cost
+ * plus the search cost of its path), search_cost = SearchNode::_searchCost */
+int bcu_fetch_plan(bcu_engine* e, int64_t offset, int64_t n, int32_t* state_idx, float* vx, float* vy, uint64_t* search_cost,
+                   uint64_t* cost);
+/* simulate the planned strikes (as bcu_evaluate on them: results, bcu_topk, bcu_level_select, bcu_gather afterwards) */
+int bcu_evaluate_plan(bcu_engine* e, const bcu_results* out);
 
 /* ---- measurement hooks -------------------------------------------------------------------------------- */
 /* CUDA-event timer on the engine's stream (the stream every kernel of this library is launched on) */
