@@ -559,6 +559,8 @@ def search_workloads(eng, W, rank, world, dist):
         assert res["digest"] == res["digest_exact"], "reach bound on / off find different solutions"
         out[name] = res
 
+    if world == 1:
+        out["planner"] = planner_workload(eng, W)
     pos, types = W.snooker22_open()
     d4, s4 = W.grid(32, 32)
     run("config4", "config 4: snooker 22-ball frame, 4-break search, beam 1024 x (32 directions x 32 speeds) = 1 048 576 strikes per "
@@ -569,6 +571,40 @@ def search_workloads(eng, W, rank, world, dist):
         d3, s3 = W.grid(256, 16)
         run("config3", "config 3: pool 16-ball layout (seed 16), 3-break beam search, beam 1024 x (256 directions x 16 speeds) = "
             "4 194 304 strikes in level 3, 'repeat' rules", p3, t3, 3, 1024, d3, s3, RepeatRules())
+    return out
+
+
+def planner_workload(eng, W):
+    """The reference's geometric planner on the device (bcu_plan) + the simulation of what it plans (bcu_evaluate_plan): config 1
+    (the reference's own test layout, one state) and a beam of 1024 random 16-ball states planned in one call.  Device time by
+    CUDA events on the engine's stream; the reference plans one state at a time on the host (1 700 expansions, ~47 ms)."""
+    import json as _json
+    tbl = W.default_table()
+    eng.set_planner(tbl, velocity_multiply=True)
+    red = 1 << W.TYPE_CODE["RED"]
+    out = {}
+    with open(os.path.join(ROOT, "tests", "golden", "layouts.json")) as f:
+        lay = _json.load(f)["test_01"]
+    p1 = np.array([b["position"] for b in lay["balls"]], np.float32)
+    t1 = np.array([W.TYPE_CODE[b["type"]] for b in lay["balls"]], np.int32)
+    tp, tt = W.random_tables(1024, 16, seed0=5000)
+    for name, pos, types, desc in (("config1", p1[None], t1[None], "config 1: 8-ball layout 00_test_01 of test/billiard_search, single-break search, "
+                                    "candidates = the reference planner's own (direct + up to 3 cushions, 3 speeds)"),
+                                   ("beam1024", tp, tt, "1024 random 16-ball states (seeds 5000..6023) planned and simulated in one call each")):
+        eng.set_states(pos, types, red)
+        eng.set_prune(0)
+        n = eng.plan()
+        res = eng.evaluate_plan(final_pos=False)
+        plan_ms, eval_ms = [], []
+        for _ in range(5):
+            eng.timer_begin(); eng.plan(); plan_ms.append(eng.timer_end())
+            eng.timer_begin(); eng.evaluate_plan(final_pos=False); eval_ms.append(eng.timer_end())
+        valid = int(((res["flags"] & 2) != 0).sum())
+        out[name] = dict(workload=desc, states=int(len(pos)), strikes_planned=int(n), valid_strikes=valid,
+                         best_cost=int(res["cost"][(res["flags"] & 2) != 0].min()) if valid else None,
+                         plan_ms=float(np.median(plan_ms)), evaluate_ms=float(np.median(eval_ms)),
+                         states_per_sec=len(pos) / ((np.median(plan_ms) + np.median(eval_ms)) * 1e-3))
+    eng.set_prune(1)
     return out
 
 

@@ -1,8 +1,12 @@
 // plan_kernel: the reference's geometric planner (bcu_planner.cuh) over every state of the beam at once.
 //
-// One thread per (state, search pocket, first ball, first link) -- the first link being the direct one or one rail combination
-// of one to three cushions (1 + 3 x rails-in-search variants) -- enumerates everything below that first search node depth first
-// and emits the strikes of every path that reaches the cue ball.  Integer / FP32 / a little FP64 scalar work with long
+// One thread per (state, search pocket, first ball, first link, second ball) -- the first link being the direct one or one rail
+// combination of one to three cushions (1 + 3 x rails-in-search variants) -- builds that first search node and enumerates
+// everything below its child for the second ball depth first, emitting the strikes of every path that reaches the cue ball.
+// The second ball is the fastest-running index, so the lanes of a warp share the first node (one converged instruction
+// stream up to it) and fan out over its children; a first node that is not feasible retires its 16-32 lanes at once.  (With
+// the first link as the unit, profiles/r02_plan_count_kernel_ncu_full.txt showed ONE active lane per warp: a feasible first
+// node carries a whole subtree, its neighbours nothing.)  Integer / FP32 / a little FP64 scalar work with long
 // divergent paths: not a throughput kernel; what matters is that the candidate lists of a whole beam never leave the device
 // (the reference plans one state at a time on the host: ~1 700 expansions, 47 ms per state).
 //
@@ -34,19 +38,21 @@ struct WriteEmit {
 };
 
 struct PlanWork {   // decode of a work item index
-    int state, pocket, only;
+    int state, pocket;
+    PlanFilter filter;
 };
 __device__ __forceinline__ bool plan_decode(const PlanTable& tb, int nStates, int nBalls, int64_t w, PlanWork* out) {
     const int variants = 1 + PLAN_BANK_INDIRECTION * tb.nSetOrder;
-    const int64_t total = (int64_t)nStates * tb.nPockets * nBalls * variants;
+    const int64_t total = (int64_t)nStates * tb.nPockets * nBalls * variants * nBalls;
     if (w >= total) return false;
+    const int second = (int)(w % nBalls); w /= nBalls;
     const int v = (int)(w % variants); w /= variants;
     const int ball = (int)(w % nBalls); w /= nBalls;
     out->pocket = (int)(w % tb.nPockets);
     out->state = (int)(w / tb.nPockets);
     const int depth = v == 0 ? 0 : 1 + (v - 1) / tb.nSetOrder;
     const int combo = v == 0 ? 0 : (v - 1) % tb.nSetOrder;
-    out->only = (ball * (PLAN_BANK_INDIRECTION + 1) + depth) * MAX_RAILS + combo;
+    out->filter.ball = ball; out->filter.depth = depth; out->filter.combo = combo; out->filter.nextBall = second;
     return true;
 }
 
@@ -57,7 +63,8 @@ __device__ __forceinline__ void plan_item(const PlanTable& tb, const StateTable&
     st.pos = states.pos + (size_t)wk.state * states.nBalls * 2;
     st.type = states.type + (size_t)wk.state * states.nBalls;
     st.searchMask = states.expectedMask[wk.state];
-    plan_root(tb, st, wk.pocket, stateBase ? stateBase[wk.state] : 0ull, phys_const(), emit, wk.only);
+    if ((st.searchMask >> tb.cueType) & 1u) return;   // isValidSearch (billiard_search.cpp:100-120): the cue ball is never searched for
+    plan_root(tb, st, wk.pocket, stateBase ? stateBase[wk.state] : 0ull, phys_const(), emit, wk.filter);
 }
 
 // pass 0: strikes per work item and per block
@@ -125,7 +132,7 @@ __global__ void __launch_bounds__(PLAN_BLOCK) plan_write_kernel(const PlanTable*
 }  // namespace
 
 int64_t plan_work_items(const PlanTable& tb, int nStates, int nBalls) {
-    return (int64_t)nStates * tb.nPockets * nBalls * (1 + PLAN_BANK_INDIRECTION * tb.nSetOrder);
+    return (int64_t)nStates * tb.nPockets * nBalls * (1 + PLAN_BANK_INDIRECTION * tb.nSetOrder) * nBalls;
 }
 
 cudaError_t launch_plan_count(const PlanTable* dTable, const PlanTable& hTable, const StateTable& states, const uint64_t* stateBase,

@@ -406,28 +406,34 @@ BCU_HD bool plan_make_node(const PlanTable& tb, const PlanState& st, const PlanN
 // Everything below one search node (expandSearchNode :299-310): every unused ball (at the pocket root: every ball of a searched
 // type), direct and over the cushions, depth first until the cue ball closes a path.  LEVEL = _searchDepth of the children;
 // a child that is not the cue ball is expanded only while LEVEL < MAX_SEARCH_DEPTH (:224-244), so the recursion is three
-// nested instantiations.  `only` >= 0 restricts the children to one (ball, cushions, combination) triple -- the unit of
-// parallel work on the device: only = (ball * (BANK_INDIRECTION + 1) + cushions) * MAX_RAILS + combination.
+// nested instantiations.  A PlanFilter restricts the enumeration to one slice of the tree -- the unit of parallel work on the
+// device: the first link (ball, number of cushions, combination) and the ball of the second link.
+struct PlanFilter {
+    int ball = -1, depth = -1, combo = -1;   // children of this node: only this (ball, cushions, combination); -1 = all
+    int nextBall = -1;                       // grandchildren: only this ball; -1 = all
+};
 template <int LEVEL, class Emit>
 BCU_HD void plan_children(const PlanTable& tb, const PlanState& st, const PlanNode& parent, const PlanNode* const* path, int nPath,
-                          uint32_t usedMask, const PhysConst& pc, Emit& emit, int only = -1) {
+                          uint32_t usedMask, const PhysConst& pc, Emit& emit, const PlanFilter& filter) {
     PlanCombos combos;
     v2 bankTarget;
     if (parent.root) bankTarget = mk(tb.pockets[parent.pocket].px, tb.pockets[parent.pocket].py);
     else bankTarget = plan_parent_target(tb, parent);
-    const int onlyBall = only >= 0 ? only / ((PLAN_BANK_INDIRECTION + 1) * MAX_RAILS) : -1;
-    const int onlyDepth = only >= 0 ? (only / MAX_RAILS) % (PLAN_BANK_INDIRECTION + 1) : -1;
-    const int onlyCombo = only >= 0 ? only % MAX_RAILS : -1;
+    PlanFilter below;
+    below.ball = filter.nextBall;
     for (int depth = 0; depth <= PLAN_BANK_INDIRECTION; ++depth) {   // 0 = direct (expandSearchNodeByBalls), 1.. = banks
-        if (onlyDepth >= 0 && depth != onlyDepth) continue;
+        if (filter.depth >= 0 && depth != filter.depth) continue;
         if (depth > 0) plan_rail_combinations(tb, depth, bankTarget, &combos);
         const int nVariants = depth == 0 ? 1 : combos.n;
         for (int c = 0; c < nVariants; ++c) {
-            if (onlyCombo >= 0 && c != onlyCombo) continue;
+            if (filter.combo >= 0 && c != filter.combo) continue;
             for (int b = 0; b < st.nBalls; ++b) {
-                if (onlyBall >= 0 && b != onlyBall) continue;
+                if (filter.ball >= 0 && b != filter.ball) continue;
                 if (st.type[b] < 0 || ((usedMask >> b) & 1u)) continue;
                 if (parent.root && !((st.searchMask >> st.type[b]) & 1u)) continue;   // :319-322, :1052-1053
+                // a node of the last level is never expanded (:224-244), so only the cue ball can contribute there: the reference
+                // builds the other nodes and drops them, which is most of its work
+                if (LEVEL == PLAN_MAX_SEARCH_DEPTH && st.type[b] != tb.cueType) continue;
                 PlanNode node;
                 if (!plan_make_node(tb, st, parent, b, depth == 0, depth == 0 ? mk(0.0f, 0.0f) : combos.target[c], depth, &node)) continue;
                 const PlanNode* sub[PLAN_MAX_SEARCH_DEPTH];
@@ -436,7 +442,7 @@ BCU_HD void plan_children(const PlanTable& tb, const PlanState& st, const PlanNo
                 if (st.type[b] == tb.cueType) {
                     plan_emit_strikes(tb, sub, nPath + 1, node, pc, emit);
                 } else if constexpr (LEVEL < PLAN_MAX_SEARCH_DEPTH) {
-                    plan_children<LEVEL + 1>(tb, st, node, sub, nPath + 1, usedMask | (1u << b), pc, emit);
+                    plan_children<LEVEL + 1>(tb, st, node, sub, nPath + 1, usedMask | (1u << b), pc, emit, below);
                 }
             }
         }
@@ -445,13 +451,14 @@ BCU_HD void plan_children(const PlanTable& tb, const PlanState& st, const PlanNo
 
 // One pocket root of one state (addPocketsAsInitialTargets :246-271): cost = the state's accumulated cost, searchCost = 0.
 template <class Emit>
-BCU_HD void plan_root(const PlanTable& tb, const PlanState& st, int pocket, uint64_t baseCost, const PhysConst& pc, Emit& emit, int only = -1) {
+BCU_HD void plan_root(const PlanTable& tb, const PlanState& st, int pocket, uint64_t baseCost, const PhysConst& pc, Emit& emit,
+                      const PlanFilter& filter = PlanFilter()) {
     PlanNode root;
     root.nEv = 0; root.ball = -1; root.pocket = pocket; root.root = true;
     root.cost = baseCost; root.searchCost = 0;
     const PlanNode* path[PLAN_MAX_SEARCH_DEPTH];
     path[0] = nullptr;
-    plan_children<1>(tb, st, root, path, 0, 0u, pc, emit, only);
+    plan_children<1>(tb, st, root, path, 0, 0u, pc, emit, filter);
 }
 
 // ---- host side: the planner's tables from the caller's description (bcu_set_planner; tests build the same tables) -------
