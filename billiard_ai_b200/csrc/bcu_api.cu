@@ -469,7 +469,15 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
         for (int64_t wave = 0; wave < nParts; wave += G) {
             for (;;) {
                 const size_t wsBytes = pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, nullptr);
-                CK(e->dPipeWs.reserve(wsBytes * G));
+                {   // a captured graph must not outlive the allocation its memset / copy / kernel nodes point into: a later
+                    // allocation at the same address is a different allocation to the driver (cuGraphLaunch crashed on it)
+                    const size_t capBefore = e->dPipeWs.cap;
+                    CK(e->dPipeWs.reserve(wsBytes * G));
+                    if (e->dPipeWs.cap != capBefore) {
+                        for (auto& kv : e->pipeGraphs) cudaGraphExecDestroy(kv.second);
+                        e->pipeGraphs.clear();
+                    }
+                }
                 // this wave's parameter blocks
                 LaunchParams hp[PIPE_MAX_STREAMS];
                 for (int g = 0; g < G; ++g) {
