@@ -425,9 +425,13 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                 const uint32_t en = sEnt[(c2 >> 6) & (ITEM_BLOCK - 1)];
                 const int o = (int)(c2 & 31u), b = (int)(en & 31u);
                 const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
-                const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2], y2 = w.vel[g2], z2 = w.acc[g2];
+                const bool partnerDynamic = (c2 & 32u) != 0;   // a resting partner is position only (rest_ball(), bcu_pipeline.cu)
+                const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2];
+                float2 y2 = make_float2(0.f, 0.f), z2 = make_float2(0.f, 0.f);
+                if (partnerDynamic) { y2 = w.vel[g2]; z2 = w.acc[g2]; }
+                const v2 a2 = partnerDynamic ? mk(z2.x, z2.y) : rest_acc(p_phys);
                 float co[5];
-                collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), mk(z2.x, z2.y), mk(y2.x, y2.y),
+                collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), a2, mk(y2.x, y2.y),
                                        mk(x2.x, x2.y), diameter, co);
                 const uint64_t j = (uint64_t)sJobBase + iq;
                 if (j < w.jobCap) {

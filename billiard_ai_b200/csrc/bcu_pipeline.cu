@@ -75,6 +75,9 @@ __device__ __forceinline__ bool kind_dynamic(int kind) {
     return kind == K_SHOT || kind == K_MOVING || kind == K_COLLISION || kind == K_RAIL;
 }
 
+// acceleration of a ball at rest: the BallState ctor's accelerationLength * normalize(0) = (-0, -0) (type.cpp:176-184)
+__device__ __forceinline__ v2 rest_acc(const PhysConst& pc) { return pc.slideAccLen * mk(0.0f, 0.0f); }
+
 struct Candidate {
     int sIdx;
     float vx, vy;
@@ -173,14 +176,19 @@ __device__ __forceinline__ void init_body(AppendShared& ash, const LaunchParams&
                         restMask |= 1u << b;
                     }
                 }
-                derive_ball(vel, false, pc, &vn, &acc);
                 const int64_t g = (int64_t)b * n + s;
                 w.pos[g] = make_float2(pos.x, pos.y);
-                w.vel[g] = make_float2(vel.x, vel.y);
-                w.vn[g] = make_float2(vn.x, vn.y);
-                w.acc[g] = make_float2(acc.x, acc.y);
-                w.nextRolling[g] = nextRolling;
                 w.meta[g] = make_meta(kind, false, -1, type);
+                // A ball at rest is position + meta: its velocity (0, 0), normalised velocity (0, 0), acceleration (-0, -0) and
+                // "no rolling time" are constants of the BallState ctor (rest_ball()), so they are neither written here nor read
+                // back (880 -> 292 bytes per 22-ball strike: the level's DRAM traffic was 6 x its algorithmic bytes)
+                if (kind == K_SHOT) {
+                    derive_ball(vel, false, pc, &vn, &acc);
+                    w.vel[g] = make_float2(vel.x, vel.y);
+                    w.vn[g] = make_float2(vn.x, vn.y);
+                    w.acc[g] = make_float2(acc.x, acc.y);
+                    w.nextRolling[g] = nextRolling;
+                }
                 if (kind == K_SHOT) {
                     offer(key, time_to_stop(acc, vel), make_code(b, CAT_REST, 0));
                     if (nextRolling >= 0.0f) offer(key, nextRolling, make_code(b, CAT_ROLLING, 0));
@@ -259,6 +267,18 @@ __device__ __forceinline__ BallRec load_ball(const PipeWorkspace& w, int64_t g) 
     r.pos = mk(q0.x, q0.y); r.vel = mk(q1.x, q1.y); r.vn = mk(q2.x, q2.y); r.acc = mk(q3.x, q3.y);
     r.nextRolling = w.nextRolling[g];
     r.kind = meta_kind(m); r.rolling = meta_rolling(m); r.lastRail = meta_last_rail(m); r.type = meta_type(m);
+    return r;
+}
+// A ball at rest (kind REST since init, or after a REST event): only position and meta are kept current in the workspace;
+// the rest of its BallState is what the ctor derives from a zero velocity (type.cpp:176-184): normalised velocity (0, 0),
+// acceleration = slideAccelerationLength * (0, 0) = (-0, -0), not rolling, no rolling time (System::append, type.cpp:510-512).
+__device__ __forceinline__ BallRec load_rest_ball(const PipeWorkspace& w, int64_t g, const PhysConst& pc) {
+    BallRec r;
+    const float2 q0 = w.pos[g];
+    const uint32_t m = w.meta[g];
+    r.pos = mk(q0.x, q0.y); r.vel = mk(0.f, 0.f); r.vn = mk(0.f, 0.f); r.acc = rest_acc(pc);
+    r.nextRolling = -1.0f;
+    r.kind = meta_kind(m); r.rolling = false; r.lastRail = meta_last_rail(m); r.type = meta_type(m);
     return r;
 }
 __device__ __forceinline__ void store_ball(const PipeWorkspace& w, int64_t g, const BallRec& r) {
@@ -342,7 +362,7 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
                 const bool pairEv = cat == CAT_STATIC_PAIR || cat == CAT_DYNAMIC_PAIR;
                 const int64_t gB = (int64_t)(pairEv ? evPartner : evBall) * w.n + s;
                 BallRec A = load_ball(w, gA);
-                BallRec B = load_ball(w, gB);
+                BallRec B = cat == CAT_STATIC_PAIR ? load_rest_ball(w, gB, pc) : load_ball(w, gB);
                 const v2 npos = advance_position(A.acc, A.vel, dt, A.pos);
                 const v2 nvel = advance_velocity(A.acc, A.vel, dt);
                 int cause = -1;

@@ -507,3 +507,54 @@ def test_evaluate_level_equals_evaluate_then_select(engine):
     for key in ("cost", "id", "potted"):
         assert np.array_equal(beam_a[key], beam_b[key]), key
     assert np.array_equal(beam_a["final_pos"].view(np.uint32), beam_b["final_pos"].view(np.uint32))
+
+
+def test_two_engines_on_two_threads_do_not_share_state(table, port):
+    """include/billiard_cuda.h: "all state lives in the engine ... different engines may be used from different threads at the
+    same time".  Two engines with different ball counts, launch shapes and prune modes run levels concurrently from two
+    threads (ctypes releases the GIL inside the calls); each must return what it returns alone."""
+    import threading
+    from billiard_ai_b200 import Engine, workloads as W
+    from billiard_ai_b200.workloads import SNOOKER_SCORES
+
+    def make(n_balls, seed, prune):
+        e = Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+        e.set_prune(prune)
+        pos, types = W.random_layout(n_balls, seed)
+        return e, pos, types
+
+    jobs = [make(16, 41, 0), make(9, 42, 1)]
+    grids = [W.grid(96, 16), W.grid(64, 24)]
+
+    def level(i):
+        e, pos, types = jobs[i]
+        e.set_states(pos, types, 1 << TYPE_CODE["RED"])
+        e.evaluate_grid(*grids[i], W.GRID_SEARCH_COST)
+        r = e.fetch()
+        tc, ti = e.topk(64)
+        return r["cost"].copy(), r["flags_raw"].copy(), r["final_pos"].copy(), tc, ti
+
+    try:
+        alone = [level(0), level(1)]
+        results = [[None] * 6, [None] * 6]
+
+        def worker(i):
+            for k in range(6):
+                results[i][k] = level(i)
+        threads = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for i in range(2):
+            for k in range(6):
+                assert all(np.array_equal(a, b) for a, b in zip(alone[i], results[i][k])), (i, k)
+        # and against the oracle, so that "the same" is also "right"
+        e, pos, types = jobs[0]
+        vx, vy = W.grid_velocities(*grids[0])
+        ora = port.evaluate(pos[None], types[None], 1 << TYPE_CODE["RED"], 0, vx, vy, W.GRID_SEARCH_COST, 0, threads=4)
+        clean = ora["min_gap"] >= 1e-9
+        assert np.array_equal(alone[0][0][clean], ora["cost"][clean])
+    finally:
+        for e, _, _ in jobs:
+            e.close()
