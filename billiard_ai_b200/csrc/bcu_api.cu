@@ -523,6 +523,8 @@ static int run(bcu_engine* e, const LaunchParams& p, bool trace, const bcu_resul
                         ws.base = e->dPipeWs.p + wsBytes * g;
                         pipeline_workspace_bytes(per, nBalls, e->jobsPerStrike, &ws);
                         ws.pruneMode = e->pruneMode;
+                        ws.table = e->dTable.p; ws.nBalls = nBalls; ws.nRails = e->table.nRails; ws.nPockets = e->table.nPockets;
+                        ws.diameter = e->table.diameter;
                         CK(cudaStreamWaitEvent(e->pipeStream[g], e->pipeFork, 0));
                         CK(launch_pipeline(e->dPipeParams.p + g, nBalls, e->table.nRails, e->table.nPockets, withCounters, ws, e->sms, e->pipeStream[g], true, e->pipeCfg));
                         // the quartic job queue is sized for the common case; a round that posts more jobs raises a flag

@@ -137,17 +137,17 @@ struct ItemShared {
 };
 
 // table geometry -> shared memory; depends on nothing a kernel of the launch writes
-__device__ __forceinline__ void items_prologue(ItemShared& sh, const LaunchParams& p) {
+__device__ __forceinline__ void items_prologue(ItemShared& sh, const PipeWorkspace& w) {
     const int tid = threadIdx.x;
-    const int R = p.table->nRails, P = p.table->nPockets;
+    const int R = w.nRails, P = w.nPockets;
     for (int i = tid; i < R; i += ITEM_BLOCK) {
-        const RailGeom rg = p.table->rails[i];
+        const RailGeom rg = w.table->rails[i];
         sh.rails[i] = rg;
         sh.detQV[i] = rg.sx * rg.dy - rg.sy * rg.dx;  // detQV of lineIntersectsLine (:651-723): depends on the rail only
         const float used = fabsf(rg.dx != 0.0f ? rg.dx : rg.dy);
         sh.railLenSq[i] = used >= 5.0f ? rg.dx * rg.dx + rg.dy * rg.dy : -1.0f;
     }
-    for (int i = tid; i < P; i += ITEM_BLOCK) sh.pockets[i] = p.table->pockets[i];
+    for (int i = tid; i < P; i += ITEM_BLOCK) sh.pockets[i] = w.table->pockets[i];
 }
 
 // `bid` of `nb` CTAs work on this round (items_kernel passes its grid)
@@ -163,7 +163,7 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
     const PocketGeom* sPockets = sh.pockets;
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int R = p.table->nRails, P = p.table->nPockets, NB = p.states.nBalls;
+    const int R = w.nRails, P = w.nPockets, NB = w.nBalls;
     const uint32_t nDyn = w.counts[4 * round + 1];
     if (nDyn == 0) return;
     uint16_t* qPairs = smemQ;
@@ -172,7 +172,7 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
     const uint32_t* dyn = w.dyn + (size_t)(round & 1) * w.dynCap;
     unsigned long long* key = w.key + (size_t)(round % 3) * w.n;
     uint32_t* jobCount = &w.counts[4 * round + 2];
-    const float diameter = p.table->diameter;
+    const float diameter = w.diameter;
     const float dd = diameter * diameter;
     const int prune = w.pruneMode;
     unsigned long long skipped = 0;   // counters / audit only
@@ -452,7 +452,7 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
     extern __shared__ uint16_t smemQ[];
     __shared__ ItemShared sh;
     if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    items_prologue(sh, *pp);
+    items_prologue(sh, w);
     cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
     __syncthreads();
     items_body(sh, smemQ, *pp, w, round, blockIdx.x, gridDim.x);

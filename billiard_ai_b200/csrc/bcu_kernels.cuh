@@ -83,6 +83,12 @@ struct PipeWorkspace {
     // quartic jobs of the round
     float* jobCo;              // [5][jobCap]
     uint32_t* jobCode;         // [jobCap] (strike << 5 | ball) << 6 | partner is dynamic << 5 | partner; bit 31 = audit mark
+    // constants of the launch BY VALUE (the table and the ball count do not change between launches of a captured graph: the
+    // ball count is part of its key, the table belongs to the engine).  Reading them through the LaunchParams block in device
+    // memory was two dependent memory round trips at the start of every kernel of the chain (params -> table pointer -> rails).
+    const TableGeom* table;
+    int nBalls, nRails, nPockets;
+    float diameter;
     int pdlEarly;              // kernels signal cudaTriggerProgrammaticLaunchCompletion() at once (launch_pipeline)
     int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
     int fused;                 // layout of a round: 1 = step + quartic (bcu_step.cuh; one key / T buffer), 0 = items + quartic + apply

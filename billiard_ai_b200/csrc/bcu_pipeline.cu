@@ -370,7 +370,7 @@ __device__ __forceinline__ void apply_body(AppendShared& ash, const LaunchParams
                 if (evType == E_POTTING) {                 // :1716-1746
                     A.vel = mk(0.f, 0.f); A.rolling = false; A.kind = K_POTTING;
                 } else if (evType == E_RAIL_COLLISION) {   // :1748-1786
-                    const RailGeom& rg = p.table->rails[evPartner];
+                    const RailGeom& rg = w.table->rails[evPartner];
                     A.vel = rail_collision(nvel, mk(rg.nx, rg.ny), pc);
                     A.rolling = true; A.kind = K_RAIL; cause = evPartner;
                 } else if (evType == E_REST) {             // :1788-1808
