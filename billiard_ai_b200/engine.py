@@ -428,7 +428,7 @@ class Engine:
         return int(self.lib.bcu_get_prune(self.h))
 
     def test_merge_records(self, blocks, k, n_balls):
-        """Test hook: G host record blocks (uint8 arrays, layout of distributed.view_block) -> the merged block, computed
+        """Test hook: G host record blocks (uint8 arrays, layout of include/billiard_cuda.h: bcu_test_merge_records) -> the merged block, computed
         by the device merge kernel that bcu_level_select runs after the all-gather."""
         blocks = [np.ascontiguousarray(b, dtype=np.uint8) for b in blocks]
         cat = np.ascontiguousarray(np.concatenate(blocks))

@@ -1,4 +1,6 @@
-"""Host-side statement of the multi-GPU level merge, in numpy.
+"""TEST INFRASTRUCTURE: a numpy restatement of the multi-GPU level merge -- the checker of the device
+merge kernel (tests/test_gpu_full_size.py, through bcu_test_merge_records) and of the sharding rule under gloo
+(tests/test_distributed_cpu.py).  Not part of the product.
 
 The product path does this on the device (csrc/bcu_topk.cu, csrc/bcu_merge.cu: top-k -> record block ->
 ncclAllGather -> merge).  This module restates the record-block layout and the merge rule on the host so that the

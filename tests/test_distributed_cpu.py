@@ -1,7 +1,7 @@
 """CPU tier, world size 2 over gloo: the host-side logic of the multi-GPU path -- contiguous candidate
 shards, per-rank top-k by (cost, id), all-gather of the record blocks, identical merge on every rank -- against a
 single-process answer.  The device kernels are not involved (no GPU here); the record-block layout and the merge
-rule are the ones of billiard_ai_b200/csrc/bcu_merge.cu, restated in numpy by billiard_ai_b200/distributed.py."""
+rule are the ones of billiard_ai_b200/csrc/bcu_merge.cu, restated in numpy by tests/merge_restatement.py."""
 import os
 import socket
 
@@ -10,7 +10,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from billiard_ai_b200 import distributed as D
+import merge_restatement as D
 from billiard_ai_b200 import workloads as W
 
 

@@ -141,7 +141,7 @@ def test_config5_slice_against_the_reference_build(engine, ref, port, prune):
 def _synthetic_blocks(rng, G, k, nb, fill):
     """G sorted record blocks as G ranks would pack them: many equal costs (the id decides), ranks with fewer than k
     valid entries and empty ranks (`fill[r]` = number of valid entries of rank r)."""
-    from billiard_ai_b200 import distributed as D
+    import merge_restatement as D
     blocks = []
     next_id = 0
     for r in range(G):
@@ -165,9 +165,9 @@ def _synthetic_blocks(rng, G, k, nb, fill):
 @pytest.mark.parametrize("G,k,nb", [(2, 1024, 22), (4, 1024, 22), (8, 1024, 22), (8, 100, 16), (3, 7, 5), (1, 64, 22)])
 def test_merge_records_kernel_against_the_numpy_merge(engine, G, k, nb):
     """merge_records_kernel (csrc/bcu_merge.cu) only runs behind ncclAllGather with more than one rank; the test hook
-    feeds it G host blocks.  Must equal distributed.merge_blocks byte for byte: full ranks, short ranks, empty ranks,
+    feeds it G host blocks.  Must equal merge_restatement.merge_blocks byte for byte: full ranks, short ranks, empty ranks,
     fewer than k valid entries in total."""
-    from billiard_ai_b200 import distributed as D
+    import merge_restatement as D
     rng = np.random.RandomState(G * 1000 + k)
     fills = [[k] * G,                                              # every rank full
              [max(0, k - 17 * r) for r in range(G)],               # short ranks
