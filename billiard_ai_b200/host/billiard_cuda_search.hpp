@@ -344,6 +344,11 @@ struct SearchOptions {
                                      // a request for few solutions plans (and simulates) at most this much more than the
                                      // reference's best-first order would before "enough solutions" ends it
     int prune = 0;                   // bcu_set_prune mode (0: every quartic the reference solves is solved)
+    bool devicePlanner = false;      // plan on the device as well (bcu_set_planner / bcu_plan / bcu_evaluate_plan): break by break,
+                                     // every state of a break planned and simulated in one call each, nothing of the
+                                     // reference's planner on the host.  Exhaustive per break (what the reference's best-first
+                                     // search converges to); `solutions` does not end it early, the time budget and a newer
+                                     // request do (between breaks).
 };
 
 struct SearchReport {   // what the last finished request did (diagnosis / tests)
@@ -488,6 +493,7 @@ private:
         const Configuration& config = rq.config;
         Engine& engine = engineFor(config, typeNamesOf(rq.state));
         const RulesTable& rules = engine.rules();
+        if (_options.devicePlanner) return runPlanned(rq, report, engine);
         auto searchState = std::make_shared<SearchState>(SearchState{config});   // :92-94
         searchState->_ball._accelerationLength = physics::accelerationLength();
         searchState->_ball._slideAccelerationLength = physics::slideAccelerationLength();
@@ -692,6 +698,159 @@ private:
                 }
             }
             for (auto& s : solutions) result.push_back(s.node->allSimulations());   // type.hpp:525-537
+        }
+        report.ms = elapsedMs();
+        return result;
+    }
+
+    // The same search with the planner on the device: level-synchronous over breaks.  A strike of break b is one entry of
+    // `strikes` (its frame, velocity, accumulated cost, the strike of break b - 1 it follows).
+    Result runPlanned(Request& rq, SearchReport& report, Engine& engine) {
+        using clock = std::chrono::steady_clock;
+        const auto t0 = clock::now();
+        auto elapsedMs = [&] { return std::chrono::duration<double, std::milli>(clock::now() - t0).count(); };
+        const Configuration& config = rq.config;
+        const RulesTable& rules = engine.rules();
+        bcu_engine* e = engine.handle();
+        Result result;
+        PlannerTables tables = PlannerTables::from(config);
+        engine.checked(bcu_set_planner(e, &tables.desc), "bcu_set_planner");
+        struct PlannedFrame { State state{std::vector<Ball>{}}; std::vector<std::string> searched; uint64_t cost = 0; int parentStrike = -1; };
+        struct PlannedStrike { int frame; glm::vec2 velocity; uint64_t cost; int parent; };
+        std::vector<PlannedFrame> allFrames;       // every frame of every break (index = id)
+        std::vector<PlannedStrike> strikes;        // every valid strike
+        std::vector<std::pair<uint64_t, int>> solutions;   // (cost, last strike)
+        std::vector<int> level;                    // frames of the current break
+        {
+            PlannedFrame root;
+            root.state = rq.state;
+            if (!rq.search._types.empty()) root.searched = rq.search._types;
+            else for (auto& b : rq.state._balls) if (b._id == rq.search._id) root.searched = {b._type};   // getTypeOf (:1994-2000)
+            allFrames.push_back(root);
+            level.push_back(0);
+        }
+        const int breaks = config._depthSearchEnabled ? _options.breaks : 1;
+        auto upload = [&](const std::vector<int>& frames, int& slots, bool withMask) {
+            slots = 0;
+            for (int f : frames) slots = std::max(slots, (int)allFrames[f].state._balls.size());
+            if (slots > BCU_MAX_BALLS) throw std::runtime_error("billiard::search::cuda: more than 32 balls");
+            const size_t nF = frames.size();
+            std::vector<float> pos(nF * slots * 2, 0.0f);
+            std::vector<int32_t> types(nF * slots, -1);
+            std::vector<uint32_t> mask(nF, withMask ? 0u : 0xffffffffu);
+            std::vector<uint64_t> base(nF, 0);
+            for (size_t i = 0; i < nF; ++i) {
+                const PlannedFrame& fr = allFrames[frames[i]];
+                for (size_t b = 0; b < fr.state._balls.size(); ++b) {
+                    pos[(i * slots + b) * 2] = fr.state._balls[b]._position.x;
+                    pos[(i * slots + b) * 2 + 1] = fr.state._balls[b]._position.y;
+                    types[i * slots + b] = rules.code(fr.state._balls[b]._type);
+                }
+                if (withMask) for (auto& t : fr.searched) { const int c = rules.code(t); if (c >= 0) mask[i] |= 1u << c; }
+                base[i] = fr.cost;
+            }
+            engine.checked(bcu_set_states(e, (int32_t)nF, slots, pos.data(), types.data(), mask.data(), base.data()), "bcu_set_states");
+        };
+        for (int brk = 0; brk < breaks && !level.empty(); ++brk) {
+            if (cancelled()) { report.cancelled = true; return result; }
+            if (elapsedMs() >= (double)_options.maxDurationMs) { report.noTimeLeft = true; break; }
+            int slots = 0;
+            upload(level, slots, true);
+            int64_t n = 0;
+            engine.checked(bcu_plan(e, &n), "bcu_plan");
+            report.batches++;
+            if (n == 0) { level.clear(); break; }
+            std::vector<int32_t> sidx((size_t)n);
+            std::vector<float> vx((size_t)n), vy((size_t)n), ftime((size_t)n), fpos((size_t)n * slots * 2);
+            std::vector<uint64_t> cost((size_t)n);
+            std::vector<uint32_t> flags((size_t)n), potted((size_t)n);
+            engine.checked(bcu_fetch_plan(e, 0, n, sidx.data(), vx.data(), vy.data(), nullptr, nullptr), "bcu_fetch_plan");
+            bcu_results out{cost.data(), flags.data(), potted.data(), ftime.data(), fpos.data(), nullptr};
+            engine.checked(bcu_evaluate_plan(e, &out), "bcu_evaluate_plan");
+            report.simulations += (size_t)n;
+            std::vector<int> next;
+            for (int64_t i = 0; i < n; ++i) {
+                if (!(flags[i] & BCU_F_COMPLETED) || !(flags[i] & BCU_F_VALID)) continue;
+                const int frameId = level[sidx[i]];
+                const PlannedFrame& fr = allFrames[frameId];
+                const int strikeId = (int)strikes.size();
+                strikes.push_back(PlannedStrike{frameId, glm::vec2{vx[i], vy[i]}, cost[i], fr.parentStrike});
+                bool solution = true;
+                if (config._depthSearchEnabled && brk + 1 < breaks) {   // simCount < BREAKS (:1407)
+                    std::vector<Ball> rest;
+                    std::unordered_map<std::string, std::string> idsByType;
+                    for (size_t b = 0; b < fr.state._balls.size(); ++b) {
+                        const Ball& ball = fr.state._balls[b];
+                        if (!((potted[i] >> b) & 1u))
+                            rest.emplace_back(glm::vec2{fpos[((size_t)i * slots + b) * 2], fpos[((size_t)i * slots + b) * 2 + 1]}, ball._type, ball._id);
+                        if (!idsByType.count(ball._type)) idsByType.insert({ball._type, ball._id});
+                    }
+                    State nextState{rest};
+                    Search nextSearch = config._rules._nextSearch(nextState, fr.searched);
+                    State modified = config._rules._modifyState(nextState, idsByType);
+                    if (modified._balls.empty()) { strikes.pop_back(); continue; }   // "could not replace all balls!" (:1432-1435)
+                    bool hasTypeToSearch = false;
+                    for (auto& ball : modified._balls)
+                        if ((hasTypeToSearch = std::count(nextSearch._types.begin(), nextSearch._types.end(), ball._type) > 0)) break;
+                    if (hasTypeToSearch) {
+                        solution = false;
+                        PlannedFrame nf;
+                        nf.state = modified;
+                        std::sort(nf.state._balls.begin(), nf.state._balls.end(), [](const Ball& a, const Ball& b) { return a._id < b._id; });
+                        nf.searched = nextSearch._types;
+                        nf.cost = cost[i];
+                        nf.parentStrike = strikeId;
+                        next.push_back((int)allFrames.size());
+                        allFrames.push_back(std::move(nf));
+                    }
+                }
+                if (solution) solutions.push_back({cost[i], strikeId});
+            }
+            level = std::move(next);
+        }
+        report.noWork = !report.noTimeLeft;
+        std::stable_sort(solutions.begin(), solutions.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        report.solutions = solutions.size();
+        for (auto& s : solutions) report.costs.push_back(s.first);
+        if (!solutions.empty()) {
+            // every strike on the path of a solution, traced once (one frame table, one bcu_trace_strikes call per 4096)
+            std::vector<int> needed;
+            std::unordered_map<int, int> slotOfStrike;
+            for (auto& s : solutions)
+                for (int k = s.second; k >= 0; k = strikes[k].parent)
+                    if (!slotOfStrike.count(k)) { slotOfStrike.insert({k, (int)needed.size()}); needed.push_back(k); }
+            std::vector<int> frames;
+            std::unordered_map<int, int> slotOfFrame;
+            for (int k : needed)
+                if (!slotOfFrame.count(strikes[k].frame)) { slotOfFrame.insert({strikes[k].frame, (int)frames.size()}); frames.push_back(strikes[k].frame); }
+            int slots = 0;
+            upload(frames, slots, false);
+            const size_t recPer = (size_t)BCU_MAX_LAYERS * slots * BCU_TRACE_REC;
+            std::vector<std::optional<node::System>> systems(needed.size());
+            for (size_t first = 0; first < needed.size(); first += 4096) {
+                const size_t m = std::min<size_t>(4096, needed.size() - first);
+                std::vector<int32_t> sidx(m), layers(m);
+                std::vector<float> vx(m), vy(m), times(m * BCU_MAX_LAYERS), rec(m * recPer);
+                for (size_t i = 0; i < m; ++i) {
+                    const PlannedStrike& st = strikes[needed[first + i]];
+                    sidx[i] = slotOfFrame.at(st.frame); vx[i] = st.velocity.x; vy[i] = st.velocity.y;
+                }
+                engine.checked(bcu_trace_strikes(e, (int32_t)m, sidx.data(), vx.data(), vy.data(), layers.data(), times.data(), rec.data()),
+                               "bcu_trace_strikes");
+                for (size_t i = 0; i < m; ++i)
+                    systems[first + i] = engine.systemFromTrace(allFrames[strikes[needed[first + i]].frame].state, layers[i],
+                                                                &times[i * BCU_MAX_LAYERS], &rec[i * recPer], slots);
+            }
+            for (auto& s : solutions) {
+                std::vector<node::System> path;
+                for (int k = s.second; k >= 0; k = strikes[k].parent) {
+                    auto& sys = systems[slotOfStrike.at(k)];
+                    if (!sys) throw std::runtime_error("billiard::search::cuda: a solution's strike did not re-simulate");
+                    path.push_back(*sys);
+                }
+                std::reverse(path.begin(), path.end());   // allSimulations(): first break first (type.hpp:525-537)
+                result.push_back(std::move(path));
+            }
         }
         report.ms = elapsedMs();
         return result;

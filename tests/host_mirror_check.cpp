@@ -184,6 +184,7 @@ extern "C" int mirror_search_check(int n, const float* pos, const char* const* t
 
         cuda::SearchOptions options;
         if (batch > 0) options.batch = (size_t)batch;
+        if (batch < 0) options.devicePlanner = true;   // batch = -1: the planner runs on the device as well
         cuda::SearchFront front{options};
         t0 = std::chrono::steady_clock::now();
         auto got = front.process(state, search, (uint16_t)solutions, conf).get();

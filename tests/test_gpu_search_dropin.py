@@ -126,3 +126,17 @@ def test_front_replaces_requests_and_honours_budget(mirror):
     assert out[1] >= 1 and out[2] == 1 and out[6] == 1
     assert out[3] == 1 and out[4] < 5000
     assert out[5] >= 3
+
+
+@pytest.mark.parametrize("case", [("test_01", 0, 1, 0), ("situation1", 0, 0, 0), ("situation1", 0, 1, 0), ("situation2", 1, 0, 2), ("situation2", 1, 0, 1)],
+                         ids=["test_01-3speeds", "situation1", "situation1-3speeds", "situation2-two-breaks-snooker", "situation2-two-breaks-repeat"])
+def test_search_with_the_device_planner_returns_the_reference_solutions(mirror, case):
+    """SearchOptions::devicePlanner: nothing of the reference's planner runs on the host -- per break every state is planned
+    (bcu_plan) and simulated (bcu_evaluate_plan) on the device, the rules between breaks stay the Configuration's own
+    std::functions.  Exhaustive per break, so it must return ALL solutions of the reference's search run to exhaustion, in
+    cost order, with identical Systems."""
+    name, depth, vm, rules_kind = case
+    r = _search(mirror, name, 65535, depth, vm, rules_kind, batch=-1)
+    assert r["ref_solutions"] > 0 and r["solutions"] == r["ref_solutions"]
+    assert r["cost_mismatches"] == 0 and r["system_mismatches"] == 0
+    assert r["costs"] == r["ref_costs"][:len(r["costs"])]
