@@ -59,6 +59,15 @@ constexpr int64_t PIPE_MAX_STRIKES = 1 << 20;   // per launch; larger batches ar
 constexpr int PIPE_MAX_STREAMS = 8;
 constexpr int PIPE_JOBS_PER_STRIKE = 8;          // initial quartic-queue capacity per strike and round; on overflow the
                                                  // launch raises a flag and the host doubles the queue and re-runs it
+// one layer's per-ball state, ball-major [nBalls][n] (the merged layout keeps two: layer k - 1 is read while layer k is written)
+struct StateBuf {
+    float2* pos;
+    float2* vel;
+    float2* vn;
+    float2* acc;
+    float* nextRolling;
+    uint32_t* meta;
+};
 struct PipeWorkspace {
     void* base;
     int64_t n;                 // strikes this layout was made for
@@ -91,6 +100,12 @@ struct PipeWorkspace {
     float diameter;
     int pdlEarly;              // kernels signal cudaTriggerProgrammaticLaunchCompletion() at once (launch_pipeline)
     int pruneMode;             // reach bound on ball pairs (bcu_items.cuh): 0 off, 1 on, 2 audit (solve everything, count failures)
+    // merged layout (bcu_round.cuh): double-buffered layer state, masks and "ball that stopped in the last event"
+    StateBuf buf[2];           // buf[0] is the single buffer of the other layouts (pos, vel, ... above)
+    uint32_t* maskDyn[2];
+    uint32_t* maskRest[2];
+    uint32_t* stopped[2];      // [n] ball that came to rest / was potted in the strike's last event (0xff: none)
+    int merged;                // layout 2
     int fused;                 // layout of a round: 1 = step + quartic (bcu_step.cuh; one key / T buffer), 0 = items + quartic + apply
 };
 // Per-engine launch configuration of the pipeline (no process-wide state: two engines on two devices or threads each
@@ -101,7 +116,9 @@ struct PipeLaunchCfg {
     size_t occSmem = ~(size_t)0;
     int occStep = 0;
     int layout = 0;            // BCU_LAYOUT: 0 = the three-kernel round (default), 1 = fused step kernel (bcu_step.cuh: bit-exact,
-                               // measured 3-4 x slower: groups of lanes per strike leave most lanes idle)
+                               // measured 3-4 x slower: groups of lanes per strike leave most lanes idle), 2 = merged round
+                               // kernel (bcu_round.cuh: apply folded into items, two kernels per round)
+    int occRound = 0;
     int stepLanes = 8;         // BCU_STEP_LANES: lanes of a warp that own one strike in step_kernel (4, 8 or 16)
     int gridPct = 100;         // BCU_GRID_PCT (experiment): grids of the round kernels as a percentage of one resident wave
     int pdlMode = 1;           // BCU_PDL: 0 off, 1 programmatic dependent launch, 2 + early trigger

@@ -179,6 +179,10 @@ __device__ __forceinline__ void init_body(AppendShared& ash, const LaunchParams&
                 const int64_t g = (int64_t)b * n + s;
                 w.pos[g] = make_float2(pos.x, pos.y);
                 w.meta[g] = make_meta(kind, false, -1, type);
+                if (w.merged) {   // balls that do not move are valid in both layer buffers
+                    w.buf[1].pos[g] = make_float2(pos.x, pos.y);
+                    w.buf[1].meta[g] = make_meta(kind, false, -1, type);
+                }
                 // A ball at rest is position + meta: its velocity (0, 0), normalised velocity (0, 0), acceleration (-0, -0) and
                 // "no rolling time" are constants of the BallState ctor (rest_ball()), so they are neither written here nor read
                 // back (880 -> 292 bytes per 22-ball strike: the level's DRAM traffic was 6 x its algorithmic bytes)
@@ -195,6 +199,7 @@ __device__ __forceinline__ void init_body(AppendShared& ash, const LaunchParams&
                 }
             }
             w.dynMask[s] = dynMask; w.restMask[s] = restMask; w.T[s] = 0.0f;
+            if (w.merged) w.stopped[0][s] = 0xffu;
             if (dynMask == 0) mark_finished(p, s, F_COMPLETED, 0, 0.0f);
         }
         // live strikes, and their dynamic balls (normally the one cue ball; further cue-type balls are appended one by one)
@@ -465,6 +470,7 @@ __global__ void __launch_bounds__(APPLY_BLOCK) apply_kernel(const LaunchParams* 
 }
 
 #include "bcu_step.cuh"
+#include "bcu_round.cuh"
 
 // rules + simulationCost + result write-out (billiard_search.cpp:1388-1405, 1473-1532; billiard_snooker.cpp:1128-1153).
 // One warp per strike, lane = ball.
@@ -480,9 +486,11 @@ __device__ __forceinline__ void finish_body(const LaunchParams& p, const PipeWor
         int kind = K_ABSENT, type = -1;
         float2 q = make_float2(0.f, 0.f);
         if (lane < NB) {
-            const uint32_t m = w.meta[(int64_t)lane * w.n + s];
+            // merged layout: the strike's last layer (layer nEvents) is in buffer nEvents & 1
+            const StateBuf& sb = w.buf[w.merged ? (int)((flags >> 8) & 1u) : 0];
+            const uint32_t m = sb.meta[(int64_t)lane * w.n + s];
             kind = meta_kind(m); type = meta_type(m);
-            q = w.pos[(int64_t)lane * w.n + s];
+            q = sb.pos[(int64_t)lane * w.n + s];
         }
         const unsigned pottedMask = __ballot_sync(FULL, kind == K_POTTING);
         const unsigned cuePotted = __ballot_sync(FULL, kind == K_POTTING && type == p.rules->cueType);
@@ -564,6 +572,10 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     const size_t oKey = take((size_t)3 * n * sizeof(unsigned long long));
     const size_t oT = take((size_t)2 * n * sizeof(float));
     const size_t oDm = take((size_t)n * sizeof(uint32_t)), oRm = take((size_t)n * sizeof(uint32_t));
+    const size_t oPos2 = take(nb * sizeof(float2)), oVel2 = take(nb * sizeof(float2)), oVn2 = take(nb * sizeof(float2));
+    const size_t oAcc2 = take(nb * sizeof(float2)), oNr2 = take(nb * sizeof(float)), oMeta2 = take(nb * sizeof(uint32_t));
+    const size_t oDm2 = take((size_t)n * sizeof(uint32_t)), oRm2 = take((size_t)n * sizeof(uint32_t));
+    const size_t oStop = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oLive = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oDyn = take((size_t)2 * w.dynCap * sizeof(uint32_t));
     const size_t oCounts = take((size_t)4 * (ROUNDS + 1) * sizeof(uint32_t));
@@ -579,12 +591,18 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
         w.live = reinterpret_cast<uint32_t*>(b + oLive); w.dyn = reinterpret_cast<uint32_t*>(b + oDyn);
         w.counts = reinterpret_cast<uint32_t*>(b + oCounts);
         w.jobCo = reinterpret_cast<float*>(b + oCo); w.jobCode = reinterpret_cast<uint32_t*>(b + oCode);
+        w.buf[0] = StateBuf{w.pos, w.vel, w.vn, w.acc, w.nextRolling, w.meta};
+        w.buf[1] = StateBuf{reinterpret_cast<float2*>(b + oPos2), reinterpret_cast<float2*>(b + oVel2), reinterpret_cast<float2*>(b + oVn2),
+                            reinterpret_cast<float2*>(b + oAcc2), reinterpret_cast<float*>(b + oNr2), reinterpret_cast<uint32_t*>(b + oMeta2)};
+        w.maskDyn[0] = w.dynMask; w.maskRest[0] = w.restMask;
+        w.maskDyn[1] = reinterpret_cast<uint32_t*>(b + oDm2); w.maskRest[1] = reinterpret_cast<uint32_t*>(b + oRm2);
+        w.stopped[0] = reinterpret_cast<uint32_t*>(b + oStop); w.stopped[1] = w.stopped[0] + n;
         *layout = w;
     }
     return off;
 }
 
-int pipeline_launch_count(const PipeLaunchCfg& cfg) { return cfg.layout == 1 ? 2 + (ROUNDS + 1) + ROUNDS : 2 + 3 * ROUNDS; }
+int pipeline_launch_count(const PipeLaunchCfg& cfg) { return cfg.layout != 0 ? 2 + (ROUNDS + 1) + ROUNDS : 2 + 3 * ROUNDS; }
 
 // One launch of the batch path over p->nCand <= w.n strikes.  `p` is a DEVICE pointer (the kernels read their parameters
 // from memory, so a captured CUDA graph of this sequence stays valid from call to call); all grids are persistent and
@@ -592,6 +610,8 @@ int pipeline_launch_count(const PipeLaunchCfg& cfg) { return cfg.layout == 1 ? 2
 cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int nPockets, bool withCounters,
                             const PipeWorkspace& wsIn, int sms, cudaStream_t stream, bool resetOverflow, PipeLaunchCfg& cfg) {
     PipeWorkspace w = wsIn;
+    w.fused = cfg.layout == 1;
+    w.merged = cfg.layout == 2;
     cudaError_t e;
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
@@ -610,6 +630,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // persistent grids: exactly one resident wave of every kernel
     int& occItems = cfg.occItems; int& occQuartic = cfg.occQuartic; int& occApply = cfg.occApply;
     size_t& occSmem = cfg.occSmem;
+    const size_t roundSmem = (size_t)2 * RK_SLOTS * nBalls * sizeof(uint16_t);
     const int lanes = cfg.stepLanes == 4 ? 4 : cfg.stepLanes == 16 ? 16 : 8;
     const size_t stepSmem = (size_t)(STEP_BLOCK / lanes) * step_group_bytes(nBalls);
     auto stepKernel = lanes == 4 ? step_kernel<4> : lanes == 16 ? step_kernel<16> : step_kernel<8>;
@@ -617,6 +638,8 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if (stepSmem > 48 * 1024) cudaFuncSetAttribute(stepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stepSmem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occStep, stepKernel, STEP_BLOCK, stepSmem);
         if (cfg.occStep < 1) cfg.occStep = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occRound, round_kernel, RK_BLOCK, roundSmem);
+        if (cfg.occRound < 1) cfg.occRound = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occItems, items_kernel, ITEM_BLOCK, itemSmem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occQuartic, quartic_kernel, QUARTIC_BLOCK, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occApply, apply_kernel, APPLY_BLOCK, 0);
@@ -647,7 +670,19 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     init_kernel<<<(unsigned)(initBlocks < sms * 8 ? initBlocks : sms * 8), 256, 0, stream>>>(p, w);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     mark();
-    w.fused = cfg.layout == 1;
+    if (w.merged) {
+        // a round is two kernels: round k applies event k of every live strike (reading layer k - 1, writing layer k) and finds
+        // the candidates of layer k in the same thread-per-dynamic-ball pass; quartic k solves the pair jobs
+        for (int k = 0; k <= ROUNDS; ++k) {
+            cudaLaunchConfig_t cr = cfgOf(sms * cfg.occRound, RK_BLOCK, roundSmem);
+            if ((e = cudaLaunchKernelEx(&cr, round_kernel, p, w, k)) != cudaSuccess) return e;
+            mark();
+            if (k == ROUNDS) break;
+            cudaLaunchConfig_t cq = cfgOf(sms * occQuartic, QUARTIC_BLOCK, 0);
+            if ((e = cudaLaunchKernelEx(&cq, quartic_kernel, w, k)) != cudaSuccess) return e;
+            mark();
+        }
+    }
     if (w.fused) {
         // a round is two kernels: step k applies event k of every live strike and collects the candidates of the new layer
         // (rest / rolling / rail / pocket times -> the strike's key, ball pairs -> quartic jobs); quartic k solves the jobs
@@ -661,7 +696,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
             mark();
         }
     }
-    for (int r = 0; r < ROUNDS && !w.fused; ++r) {
+    for (int r = 0; r < ROUNDS && !w.fused && !w.merged; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * occItems, ITEM_BLOCK, itemSmem);
         if ((e = cudaLaunchKernelEx(&ci, items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
@@ -677,7 +712,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if ((e = cudaLaunchKernelEx(&cf, finish_kernel, p, w)) != cudaSuccess) return e;
     }
     mark();
-    if (timing && w.fused) {
+    if (timing && (w.fused || w.merged)) {
         cudaStreamSynchronize(stream);
         std::vector<uint32_t> counts(4 * (ROUNDS + 1));
         cudaMemcpy(counts.data(), w.counts, counts.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost);

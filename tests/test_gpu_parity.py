@@ -558,3 +558,37 @@ def test_two_engines_on_two_threads_do_not_share_state(table, port):
     finally:
         for e, _, _ in jobs:
             e.close()
+
+
+@pytest.mark.parametrize("layout", [1, 2], ids=["fused-step-kernel", "merged-round-kernel"])
+def test_experimental_round_layouts_are_bit_identical(engine, table, layout):
+    """BCU_LAYOUT = 1 (bcu_step.cuh: a group of lanes owns a strike) and 2 (bcu_round.cuh: apply folded into items, double-buffered
+    layers): kept as measured experiments (both slower).  They must return exactly what the default three-kernel
+    round returns -- every output incl. the event log, both prune modes."""
+    from billiard_ai_b200 import Engine, workloads as W
+    pos, types = W.snooker22_open(31)
+    dirs, speeds = W.grid(256, 24)
+    vx, vy = W.grid_velocities(dirs, speeds)
+    old = os.environ.get("BCU_LAYOUT")
+    os.environ["BCU_LAYOUT"] = str(layout)
+    try:
+        other = Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+    finally:
+        if old is None:
+            os.environ.pop("BCU_LAYOUT", None)
+        else:
+            os.environ["BCU_LAYOUT"] = old
+    try:
+        for prune in (0, 1):
+            res = []
+            for e in (engine, other):
+                e.set_prune(prune)
+                e.set_states(pos, types, 1 << TYPE_CODE["RED"])
+                res.append(e.evaluate(0, vx, vy, 100000, 7, final_pos=True, event_log=True))
+            for key in ("cost", "flags_raw", "potted", "event_log"):
+                assert np.array_equal(res[0][key], res[1][key]), (layout, prune, key)
+            assert np.array_equal(res[0]["final_time"].view(np.uint32), res[1]["final_time"].view(np.uint32))
+            assert np.array_equal(res[0]["final_pos"].view(np.uint32), res[1]["final_pos"].view(np.uint32))
+    finally:
+        engine.set_prune(0)
+        other.close()
