@@ -1,6 +1,6 @@
 // plan_kernel: the reference's geometric planner (bcu_planner.cuh) over every state of the beam at once.
 //
-// One thread per (state, search pocket, first ball, first link, second ball) -- the first link being the direct one or one rail
+// One thread per (state, search pocket, first ball, first link, second ball, cushions of the second link) -- the first link being the direct one or one rail
 // combination of one to three cushions (1 + 3 x rails-in-search variants) -- builds that first search node and enumerates
 // everything below its child for the second ball depth first, emitting the strikes of every path that reaches the cue ball.
 // The second ball is the fastest-running index, so the lanes of a warp share the first node (one converged instruction
@@ -43,8 +43,9 @@ struct PlanWork {   // decode of a work item index
 };
 __device__ __forceinline__ bool plan_decode(const PlanTable& tb, int nStates, int nBalls, int64_t w, PlanWork* out) {
     const int variants = 1 + PLAN_BANK_INDIRECTION * tb.nSetOrder;
-    const int64_t total = (int64_t)nStates * tb.nPockets * nBalls * variants * nBalls;
+    const int64_t total = (int64_t)nStates * tb.nPockets * nBalls * variants * nBalls * (PLAN_BANK_INDIRECTION + 1);
     if (w >= total) return false;
+    const int secondDepth = (int)(w % (PLAN_BANK_INDIRECTION + 1)); w /= (PLAN_BANK_INDIRECTION + 1);
     const int second = (int)(w % nBalls); w /= nBalls;
     const int v = (int)(w % variants); w /= variants;
     const int ball = (int)(w % nBalls); w /= nBalls;
@@ -52,7 +53,8 @@ __device__ __forceinline__ bool plan_decode(const PlanTable& tb, int nStates, in
     out->state = (int)(w / tb.nPockets);
     const int depth = v == 0 ? 0 : 1 + (v - 1) / tb.nSetOrder;
     const int combo = v == 0 ? 0 : (v - 1) % tb.nSetOrder;
-    out->filter.ball = ball; out->filter.depth = depth; out->filter.combo = combo; out->filter.nextBall = second;
+    out->filter.ball = ball; out->filter.depth = depth; out->filter.combo = combo;
+    out->filter.nextBall = second; out->filter.nextDepth = secondDepth;
     return true;
 }
 
@@ -132,7 +134,7 @@ __global__ void __launch_bounds__(PLAN_BLOCK) plan_write_kernel(const PlanTable*
 }  // namespace
 
 int64_t plan_work_items(const PlanTable& tb, int nStates, int nBalls) {
-    return (int64_t)nStates * tb.nPockets * nBalls * (1 + PLAN_BANK_INDIRECTION * tb.nSetOrder) * nBalls;
+    return (int64_t)nStates * tb.nPockets * nBalls * (1 + PLAN_BANK_INDIRECTION * tb.nSetOrder) * nBalls * (PLAN_BANK_INDIRECTION + 1);
 }
 
 cudaError_t launch_plan_count(const PlanTable* dTable, const PlanTable& hTable, const StateTable& states, const uint64_t* stateBase,

@@ -410,7 +410,7 @@ BCU_HD bool plan_make_node(const PlanTable& tb, const PlanState& st, const PlanN
 // device: the first link (ball, number of cushions, combination) and the ball of the second link.
 struct PlanFilter {
     int ball = -1, depth = -1, combo = -1;   // children of this node: only this (ball, cushions, combination); -1 = all
-    int nextBall = -1;                       // grandchildren: only this ball; -1 = all
+    int nextBall = -1, nextDepth = -1;       // grandchildren: only this ball / this number of cushions; -1 = all
 };
 template <int LEVEL, class Emit>
 BCU_HD void plan_children(const PlanTable& tb, const PlanState& st, const PlanNode& parent, const PlanNode* const* path, int nPath,
@@ -421,6 +421,7 @@ BCU_HD void plan_children(const PlanTable& tb, const PlanState& st, const PlanNo
     else bankTarget = plan_parent_target(tb, parent);
     PlanFilter below;
     below.ball = filter.nextBall;
+    below.depth = filter.nextDepth;
     for (int depth = 0; depth <= PLAN_BANK_INDIRECTION; ++depth) {   // 0 = direct (expandSearchNodeByBalls), 1.. = banks
         if (filter.depth >= 0 && depth != filter.depth) continue;
         if (depth > 0) plan_rail_combinations(tb, depth, bankTarget, &combos);
