@@ -370,6 +370,7 @@ struct SearchReport {   // what the last finished request did (diagnosis / tests
 class SearchFront {
 public:
     using Result = std::vector<std::vector<node::System>>;
+    using NodeResult = std::vector<std::shared_ptr<SearchNode>>;
 
     explicit SearchFront(SearchOptions options = {}) : _options(options), _worker([this] { work(); }) {}
     ~SearchFront() {
@@ -396,6 +397,20 @@ public:
         return future;
     }
 
+    // == billiard::search::searchOnly (billiard_search.hpp:13-15, src :122-139): the solution SearchNodes themselves, ascending
+    // by cost; each node's path carries its SIMULATION nodes with their Systems filled in (host-planner mode only)
+    std::future<NodeResult> processNodes(const State& state, const Search& search, uint16_t solutions, const Configuration& config) {
+        auto request = std::make_unique<Request>(Request{state, search, solutions, config, std::promise<Result>{}, true, std::promise<NodeResult>{}});
+        std::future<NodeResult> future = request->nodes.get_future();
+        {
+            std::lock_guard<std::mutex> guard(_lock);
+            _pending = std::move(request);
+            _cancel = true;
+        }
+        _wake.notify_all();
+        return future;
+    }
+
     SearchReport lastReport() {
         std::lock_guard<std::mutex> guard(_lock);
         return _report;
@@ -408,6 +423,8 @@ private:
         uint16_t solutions;
         Configuration config;
         std::promise<Result> result;
+        bool wantNodes = false;       // searchOnly(): the solution nodes instead of their Systems
+        std::promise<NodeResult> nodes;
     };
     struct Open {
         std::shared_ptr<SearchNode> node;
@@ -435,13 +452,18 @@ private:
             }
             try {
                 SearchReport report;
+                _solutionNodes.clear();
                 Result result = run(*request, report);
                 std::lock_guard<std::mutex> guard(_lock);
                 _report = report;
-                if (!report.cancelled) request->result.set_value(std::move(result));
+                if (!report.cancelled) {
+                    if (request->wantNodes) request->nodes.set_value(std::move(_solutionNodes));
+                    else request->result.set_value(std::move(result));
+                }
                 // cancelled: the promise dies with the request -> broken_promise, as in the reference
             } catch (...) {
-                request->result.set_exception(std::current_exception());
+                if (request->wantNodes) request->nodes.set_exception(std::current_exception());
+                else request->result.set_exception(std::current_exception());
             }
         }
     }
@@ -698,6 +720,7 @@ private:
                 }
             }
             for (auto& s : solutions) result.push_back(s.node->allSimulations());   // type.hpp:525-537
+            for (auto& s : solutions) _solutionNodes.push_back(s.node);
         }
         report.ms = elapsedMs();
         return result;
@@ -864,8 +887,16 @@ private:
     SearchReport _report;
     std::unique_ptr<Engine> _engine;
     std::vector<float> _engineKey;
+    NodeResult _solutionNodes;   // of the request being worked on (worker thread only)
     std::thread _worker;   // last: started when everything above exists
 };
+
+// == billiard::search::searchOnly(state, search, solutions, config), billiard_search.hpp:13-15
+inline std::future<std::vector<std::shared_ptr<SearchNode>>> searchOnly(const State& state, const Search& search, uint16_t solutions,
+                                                                        const Configuration& config) {
+    static SearchFront front{};
+    return front.processNodes(state, search, solutions, config);
+}
 
 // == billiard::search::search(state, search, solutions, config), billiard_search.hpp:9-12.  Like the reference's, the
 // manager behind it is a function-local static that lives until the process exits (billiard_search.cpp:86-90).

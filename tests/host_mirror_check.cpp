@@ -225,7 +225,8 @@ extern "C" int mirror_search_check(int n, const float* pos, const char* const* t
 // flight (its future breaks its promise, as the reference's does), an invalid search and `solutions` = 0 return at once,
 // the time budget ends a request with what it has, and the free function search() returns ascending results.
 // out: [0] first future broke its promise, [1] second future's solutions, [2] invalid search returned empty, [3] budget run
-// ended by noTimeLeft, [4] ms of the budget run, [5] solutions of search(), [6] solutions = 0 returned empty.
+// ended by noTimeLeft, [4] ms of the budget run, [5] solutions of search(), [6] solutions = 0 returned empty,
+// [7] searchOnly() returned the same solutions as nodes.
 extern "C" int mirror_front_check(int n, const float* pos, const char* const* typeNames, int nTypes, const int32_t* types,
                                   int nSearchTypes, const int32_t* searchTypes, int64_t* out) {
     std::vector<std::string> names(typeNames, typeNames + nTypes);
@@ -256,7 +257,17 @@ extern "C" int mirror_front_check(int n, const float* pos, const char* const* ty
             out[4] = (int64_t)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
             out[3] = front.lastReport().noTimeLeft;
         }
-        out[5] = (int64_t)cuda::search(state, search, 3, conf).get().size();
+        auto systems = cuda::search(state, search, 3, conf).get();
+        out[5] = (int64_t)systems.size();
+        // searchOnly(): the same solutions as SearchNodes (cost ascending, Systems on their paths)
+        auto nodes = cuda::searchOnly(state, search, 3, conf).get();
+        bool same = nodes.size() == systems.size();
+        for (size_t i = 0; same && i < nodes.size(); ++i) {
+            auto sims = nodes[i]->allSimulations();
+            same = nodes[i]->_isSolution && sims.size() == systems[i].size() && (i == 0 || nodes[i - 1]->_cost <= nodes[i]->_cost);
+            for (size_t b = 0; same && b < sims.size(); ++b) same = compareSystems(sims[b], systems[i][b]) == 0;
+        }
+        out[7] = same;
         return 0;
     } catch (const std::exception& e) {
         std::fprintf(stderr, "mirror_front_check: %s\n", e.what());

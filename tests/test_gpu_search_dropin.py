@@ -126,6 +126,7 @@ def test_front_replaces_requests_and_honours_budget(mirror):
     assert out[1] >= 1 and out[2] == 1 and out[6] == 1
     assert out[3] == 1 and out[4] < 5000
     assert out[5] >= 3
+    assert out[7] == 1, "searchOnly() differs from search()"
 
 
 @pytest.mark.parametrize("case", [("test_01", 0, 1, 0), ("situation1", 0, 0, 0), ("situation1", 0, 1, 0), ("situation2", 1, 0, 2), ("situation2", 1, 0, 1)],
