@@ -1185,20 +1185,23 @@ int bcu_fetch_plan(bcu_engine* e, int64_t offset, int64_t n, int32_t* stateIdx, 
     return BCU_OK;
 }
 
-int bcu_evaluate_plan(bcu_engine* e, const bcu_results* out) {
+int bcu_evaluate_plan(bcu_engine* e, const bcu_results* out) { return bcu_evaluate_plan_range(e, 0, -1, out); }
+
+int bcu_evaluate_plan_range(bcu_engine* e, int64_t first, int64_t count, const bcu_results* out) {
     if (!e) return BCU_ERR_INVALID;
     if (e->planCount < 0) return fail(e, BCU_ERR_STATE, "bcu_evaluate_plan: no plan (bcu_plan; bcu_set_states / bcu_evaluate discard it)");
-    const int64_t n = e->planCount;
-    if (n == 0) return BCU_OK;
+    if (count < 0) count = e->planCount - first;
+    if (first < 0 || count < 0 || first + count > e->planCount) return fail(e, BCU_ERR_INVALID, "bcu_evaluate_plan_range: range");
+    const int64_t n = count;
     CK(cudaSetDevice(e->device));
     const bool wantLog = out && out->event_log;
     int rc = reserve_results(e, n, true, wantLog);
     if (rc) return rc;
     LaunchParams p;
     fill_common(e, p, n, true, wantLog);
-    p.src.stateIdx = e->dCandState.p; p.src.vx = e->dVx.p; p.src.vy = e->dVy.p;
-    p.src.searchCost = e->dSearchCost.p; p.src.baseCost = e->dBaseCost.p;
-    e->last = p; e->haveLast = true; e->lastFirst = 0;
+    p.src.stateIdx = e->dCandState.p + first; p.src.vx = e->dVx.p + first; p.src.vy = e->dVy.p + first;
+    p.src.searchCost = e->dSearchCost.p + first; p.src.baseCost = e->dBaseCost.p + first;
+    e->last = p; e->haveLast = true; e->lastFirst = first;
     bool copied = false;
     rc = run(e, p, false, out, &copied);
     if (rc) { e->haveLast = false; return rc; }

@@ -72,9 +72,8 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
     bcu_engine_rank_info(e, &rank, &world);
     const int NB = nBalls, L = sp->levels, K = sp->beam;
     // candidates of a state: the direction x speed grid, or -- n_dirs == 0 -- the strikes the reference's planner finds for it
-    // (bcu_set_planner; planned and simulated on the device, one rank)
+    // (bcu_set_planner; every rank plans the whole beam -- the plan is deterministic -- and simulates its contiguous share of it)
     const bool planned = sp->n_dirs == 0;
-    if (planned && world > 1) return BCU_ERR_INVALID;
     const int64_t perState = planned ? 0 : (int64_t)sp->n_dirs * sp->n_speeds;
     std::vector<int32_t> planState;
     std::vector<float> planVx, planVy;
@@ -123,7 +122,9 @@ extern "C" int bcu_search_levels(bcu_engine* e, int32_t nBalls, const float* pos
             planState.resize((size_t)total); planVx.resize((size_t)total); planVy.resize((size_t)total);
             rc = bcu_fetch_plan(e, 0, total, planState.data(), planVx.data(), planVy.data(), nullptr, nullptr);
             if (rc) return rc;
-            rc = total > 0 ? bcu_evaluate_plan(e, nullptr) : BCU_OK;
+            const int64_t per = (total + world - 1) / world;
+            const int64_t lo = std::min(total, (int64_t)rank * per), hi = std::min(total, lo + per);
+            rc = total > 0 ? bcu_evaluate_plan_range(e, lo, hi - lo, nullptr) : BCU_OK;
             if (rc) return rc;
         } else {
             const int64_t per = (total + world - 1) / world;

@@ -80,6 +80,7 @@ def load_library(path=None):
     lib.bcu_fetch_plan.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_float),
                                    C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.bcu_evaluate_plan.argtypes = [C.c_void_p, C.c_void_p]
+    lib.bcu_evaluate_plan_range.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
     lib.bcu_engine_rank_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.bcu_search_levels.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p,
                                       C.c_void_p]

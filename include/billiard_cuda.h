@@ -221,8 +221,8 @@ typedef struct bcu_search_params {
     int32_t levels;                /* BREAKS (billiard_search.cpp:15), 1..BCU_MAX_SEARCH_LEVELS */
     int32_t beam;                  /* strikes kept per level, 1..1024 */
     int32_t n_dirs, n_speeds;      /* the candidate grid of every state (as bcu_evaluate_grid); n_dirs = 0: the strikes the
-                                      reference's planner finds for the state instead (bcu_set_planner first; planned and
-                                      simulated on the device; one rank; dir_index / speed_index of the result are -1) */
+                                      reference's planner finds for the state instead (bcu_set_planner first; planned on every
+                                      rank, simulated in shares; dir_index / speed_index of the result are -1) */
     const float* dirs;             /* [n_dirs][2] */
     const float* speeds;           /* [n_speeds] */
     uint64_t search_cost;          /* SearchNode::_searchCost of every strike */
@@ -302,6 +302,9 @@ int bcu_fetch_plan(bcu_engine* e, int64_t offset, int64_t n, int32_t* state_idx,
                    uint64_t* cost);
 /* simulate the planned strikes (as bcu_evaluate on them: results, bcu_topk, bcu_level_select, bcu_gather afterwards) */
 int bcu_evaluate_plan(bcu_engine* e, const bcu_results* out);
+/* the same for strikes [first, first + count) of the plan (count < 0: to the end) -- a rank's contiguous share when the plan
+ * (identical on every rank: it is deterministic) is simulated on several GPUs; candidate ids stay positions in the whole plan */
+int bcu_evaluate_plan_range(bcu_engine* e, int64_t first, int64_t count, const bcu_results* out);
 
 /* ---- measurement hooks -------------------------------------------------------------------------------- */
 /* CUDA-event timer on the engine's stream (the stream every kernel of this library is launched on) */
