@@ -281,6 +281,9 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     e->pipeCfg.roundTiming = getenv("BCU_ROUND_TIMING") != nullptr;
     if (const char* pv = getenv("BCU_PDL")) e->pipeCfg.pdlMode = atoi(pv);
     if (const char* gv = getenv("BCU_GRID_PCT")) { const int v = atoi(gv); e->pipeCfg.gridPct = v < 5 ? 5 : v > 400 ? 400 : v; }
+    if (const char* dv = getenv("BCU_DENSE_MIN")) { const long long v = atoll(dv); e->pipeCfg.denseMinItems = e->pipeCfg.denseMinQuartic = v < 0 ? 0 : v; }
+    if (const char* dv = getenv("BCU_DENSE_MIN_ITEMS")) { const long long v = atoll(dv); e->pipeCfg.denseMinItems = v < 0 ? 0 : v; }
+    if (const char* dv = getenv("BCU_DENSE_MIN_QUARTIC")) { const long long v = atoll(dv); e->pipeCfg.denseMinQuartic = v < 0 ? 0 : v; }
     if (const char* lv = getenv("BCU_LAYOUT")) { const int v = atoi(lv); e->pipeCfg.layout = v == 1 ? 1 : v == 2 ? 2 : 0; }
     if (const char* lv = getenv("BCU_STEP_LANES")) e->pipeCfg.stepLanes = atoi(lv);
     e->selectTiming = getenv("BCU_SELECT_TIMING") != nullptr;

@@ -21,6 +21,9 @@ constexpr int ITEM_BLOCK = ITEM_BLOCK_V;
 #ifndef ITEM_MIN_BLOCKS
 #define ITEM_MIN_BLOCKS 6
 #endif
+#ifndef ITEM_DENSE_MIN_BLOCKS
+#define ITEM_DENSE_MIN_BLOCKS 8   // items_kernel_dense: the instantiation for large parts (see launch_pipeline)
+#endif
 
 struct ItemCounts {
     int pairs, dynPairs;
@@ -454,6 +457,17 @@ __global__ void __launch_bounds__(ITEM_BLOCK, ITEM_MIN_BLOCKS) items_kernel(cons
     if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
     items_prologue(sh, w);
     cudaGridDependencySynchronize();   // nothing above depends on the previous kernel
+    __syncthreads();
+    items_body(sh, smemQ, *pp, w, round, blockIdx.x, gridDim.x);
+}
+// The same kernel compiled for more resident CTAs per SM (fewer registers per thread): slower per thread, which is what a
+// small, latency-bound round pays for, and faster in aggregate once a round has enough work to be issue-bound.
+__global__ void __launch_bounds__(ITEM_BLOCK, ITEM_DENSE_MIN_BLOCKS) items_kernel_dense(const LaunchParams* __restrict__ pp, PipeWorkspace w, int round) {
+    extern __shared__ uint16_t smemQ[];
+    __shared__ ItemShared sh;
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    items_prologue(sh, w);
+    cudaGridDependencySynchronize();
     __syncthreads();
     items_body(sh, smemQ, *pp, w, round, blockIdx.x, gridDim.x);
 }

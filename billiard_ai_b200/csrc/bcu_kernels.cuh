@@ -115,6 +115,10 @@ struct PipeLaunchCfg {
     int occItems = 0, occQuartic = 0, occApply = 0;
     size_t occSmem = ~(size_t)0;
     int occStep = 0;
+    int occItemsDense = 0, occQuarticDense = 0;
+    // parts of this many strikes and more run items_kernel_dense / quartic_kernel_dense (BCU_DENSE_MIN sets both,
+    // BCU_DENSE_MIN_ITEMS / BCU_DENSE_MIN_QUARTIC one of them)
+    int64_t denseMinItems = 65536, denseMinQuartic = 65536;
     int layout = 0;            // BCU_LAYOUT: 0 = the three-kernel round (default), 1 = fused step kernel (bcu_step.cuh: bit-exact,
                                // measured 3-4 x slower: groups of lanes per strike leave most lanes idle), 2 = merged round
                                // kernel (bcu_round.cuh: apply folded into items, two kernels per round)

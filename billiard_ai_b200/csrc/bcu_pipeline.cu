@@ -44,6 +44,9 @@ constexpr int QUARTIC_BLOCK = 128;
 #ifndef QUARTIC_MIN_BLOCKS
 #define QUARTIC_MIN_BLOCKS 6
 #endif
+#ifndef QUARTIC_DENSE_MIN_BLOCKS
+#define QUARTIC_DENSE_MIN_BLOCKS 10   // quartic_kernel_dense: the instantiation for large parts (see launch_pipeline)
+#endif
 constexpr int APPLY_BLOCK = 256;
 
 enum Category : uint32_t { CAT_REST = 0, CAT_ROLLING = 1, CAT_STATIC_PAIR = 2, CAT_DYNAMIC_PAIR = 3, CAT_RAIL = 4, CAT_POCKET = 5 };
@@ -251,6 +254,11 @@ __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, 
 }
 
 __global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+    quartic_body(w, round, blockIdx.x, gridDim.x);
+}
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_DENSE_MIN_BLOCKS) quartic_kernel_dense(PipeWorkspace w, int round) {
     if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
     cudaGridDependencySynchronize();
     quartic_body(w, round, blockIdx.x, gridDim.x);
@@ -646,6 +654,10 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if (occItems < 1) occItems = 1;
         if (occQuartic < 1) occQuartic = 1;
         if (occApply < 1) occApply = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occItemsDense, items_kernel_dense, ITEM_BLOCK, itemSmem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occQuarticDense, quartic_kernel_dense, QUARTIC_BLOCK, 0);
+        if (cfg.occItemsDense < 1) cfg.occItemsDense = 1;
+        if (cfg.occQuarticDense < 1) cfg.occQuarticDense = 1;
         occSmem = itemSmem;
     }
     // Programmatic dependent launch: every kernel after init is launched with the stream-serialisation attribute and signals
@@ -696,12 +708,17 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
             mark();
         }
     }
+    // Parts of 65 536 strikes and more (cfg.denseMinItems / denseMinQuartic) take the instantiations of items / quartic that
+    // are compiled for more resident CTAs per SM.  Measured (profiles/r02_dense_sweep.txt): 1000 tables x 4096 strikes (parts
+    // of 2^20) 99.1 M strikes/s against 93.7 M, parts of 131 072: 96.7 against 91.3; parts of 65 536: -1 % with the reach bound,
+    // +6 % without; parts of 32 768 (the 65 536-strike level, latency-bound rounds) lose 3-5 % with them.  Same code, same results.
+    const bool denseI = w.n >= cfg.denseMinItems, denseQ = w.n >= cfg.denseMinQuartic;
     for (int r = 0; r < ROUNDS && !w.fused && !w.merged; ++r) {
-        cudaLaunchConfig_t ci = cfgOf(sms * occItems, ITEM_BLOCK, itemSmem);
-        if ((e = cudaLaunchKernelEx(&ci, items_kernel, p, w, r)) != cudaSuccess) return e;
+        cudaLaunchConfig_t ci = cfgOf(sms * (denseI ? cfg.occItemsDense : occItems), ITEM_BLOCK, itemSmem);
+        if ((e = cudaLaunchKernelEx(&ci, denseI ? items_kernel_dense : items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
-        cudaLaunchConfig_t cq = cfgOf(sms * occQuartic, QUARTIC_BLOCK, 0);
-        if ((e = cudaLaunchKernelEx(&cq, quartic_kernel, w, r)) != cudaSuccess) return e;
+        cudaLaunchConfig_t cq = cfgOf(sms * (denseQ ? cfg.occQuarticDense : occQuartic), QUARTIC_BLOCK, 0);
+        if ((e = cudaLaunchKernelEx(&cq, denseQ ? quartic_kernel_dense : quartic_kernel, w, r)) != cudaSuccess) return e;
         mark();
         cudaLaunchConfig_t ca = cfgOf(sms * occApply, APPLY_BLOCK, 0);
         if ((e = cudaLaunchKernelEx(&ca, apply_kernel, p, w, r)) != cudaSuccess) return e;
