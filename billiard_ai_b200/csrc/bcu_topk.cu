@@ -217,3 +217,82 @@ cudaError_t launch_topk(const uint64_t* cost, const uint32_t* flags, int64_t nCa
 }
 
 }  // namespace bcu
+
+// ---------------------------------------------------------------------------------------------------------------------
+// bcu_topk_static: the same selection for callers that cannot allocate (code under CUDA graph capture, serving loops and
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+//
+// The scratch of launch_topk -- the compacted list of valid keys and the per-CTA sorted lists of the streaming sorter --
+// lives in ONE file-scope device array per GPU that loads the library (held until exit): TK_LIST keys of the list plus
+// 148 lists of up to 1024 keys, 2 687 232 bytes.  Nothing in it has to start at zero: the list is written before it is read
+// up to the valid count (which lives in the caller's d_out_count, cleared here with a memset node), and every per-CTA list
+// is written whole by the CTA that owns it before the merge reads it.  Every call on a device shares the array, so two calls
+// that overlap on the GPU (different streams, no dependency) race; calls on one stream are ordered and fine.
+// ---------------------------------------------------------------------------------------------------------------------
+#include <cstdio>
+#include <mutex>
+
+#include "../../include/billiard_cuda.h"
+
+namespace bcu {
+constexpr size_t TOPK_STATIC_BYTES = (size_t)TK_LIST * sizeof(ulonglong2) + (size_t)148 * TK_CAP * 2 * sizeof(uint64_t) + 256;
+static __device__ __align__(256) unsigned char g_topkStaticScratch[TOPK_STATIC_BYTES];
+
+constexpr int TOPK_STATIC_MAX_DEVICES = 64;
+static std::mutex g_topkStaticMutex;
+static void* g_topkStaticPtr[TOPK_STATIC_MAX_DEVICES] = {};   // device address of the array on device i (0 = not asked yet)
+
+// In host code `g_topkStaticScratch` names a host-side shadow of the symbol, not device memory: the address a kernel may
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static cudaError_t topk_static_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= TOPK_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_topkStaticMutex);
+    if (!g_topkStaticPtr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_topkStaticScratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_topkStaticPtr[dev] = p;
+    }
+    *out = g_topkStaticPtr[dev];
+    return cudaSuccess;
+}
+}  // namespace bcu
+
+extern "C" int bcu_topk_static(const uint64_t* d_cost, const uint32_t* d_flags, int64_t n, int64_t first_candidate, int32_t k,
+                               uint64_t* d_out_cost, uint64_t* d_out_id, int32_t* d_out_count, void* stream,
+                               char* err, int32_t err_cap) {
+    using namespace bcu;
+    auto fail = [&](int code, const char* what, const char* detail) {
+        if (err && err_cap > 0) snprintf(err, (size_t)err_cap, "bcu_topk_static: %s%s%s", what, detail ? ": " : "", detail ? detail : "");
+        return code;
+    };
+    if (err && err_cap > 0) err[0] = 0;
+    if (!d_cost || !d_flags || !d_out_cost || !d_out_id || !d_out_count) return fail(BCU_ERR_INVALID, "null pointer argument", nullptr);
+    if (n < 0 || n > BCU_TOPK_STATIC_MAX_CANDIDATES) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "n = %lld candidates, the static scratch serves 0 .. %lld (use bcu_topk beyond that)", (long long)n,
+                 (long long)BCU_TOPK_STATIC_MAX_CANDIDATES);
+        return fail(BCU_ERR_INVALID, "size beyond the maximum", buf);
+    }
+    if (k < 1 || k > BCU_TOPK_STATIC_MAX_K) {
+        char buf[96];
+        snprintf(buf, sizeof buf, "k = %d, allowed 1 .. %d", (int)k, (int)BCU_TOPK_STATIC_MAX_K);
+        return fail(BCU_ERR_INVALID, "size beyond the maximum", buf);
+    }
+    static_assert(BCU_TOPK_STATIC_MAX_K <= TK_CAP, "k limit");
+    if (topk_scratch_bytes(n, k) > TOPK_STATIC_BYTES) return fail(BCU_ERR_INVALID, "size beyond the maximum", "scratch");
+    void* scratch = nullptr;
+    cudaError_t ce = topk_static_scratch(&scratch);
+    if (ce != cudaSuccess) {
+        const int code = (ce == cudaErrorNoDevice || ce == cudaErrorInsufficientDriver) ? BCU_ERR_NO_DEVICE : BCU_ERR_CUDA;
+        return fail(code, "cudaGetSymbolAddress", cudaGetErrorString(ce));
+    }
+    ce = launch_topk(d_cost, d_flags, n, first_candidate, k, d_out_cost, d_out_id, d_out_count, scratch, TOPK_STATIC_BYTES,
+                     (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(BCU_ERR_CUDA, "launch", cudaGetErrorString(ce));
+    return BCU_OK;
+}

@@ -89,6 +89,19 @@ def load_library(path=None):
     return lib
 
 
+def topk_static(d_cost, d_flags, n, first_candidate, k, d_out_cost, d_out_id, d_out_count, stream=0, lib=None):
+    """bcu_topk_static (include/billiard_cuda.h): top-k of (cost, id) among VALID candidates on DEVICE pointers (integers),
+    queued on `stream`, no allocation anywhere (static device scratch, hence n <= 2^22 and k <= 1024).  Engine-free; does not
+    synchronise.  Raises BcuError with the library's message."""
+    lib = lib or load_library()
+    err = C.create_string_buffer(256)
+    rc = lib.bcu_topk_static(C.c_void_p(d_cost), C.c_void_p(d_flags), C.c_int64(n), C.c_int64(first_candidate), C.c_int32(k),
+                             C.c_void_p(d_out_cost), C.c_void_p(d_out_id), C.c_void_p(d_out_count), C.c_void_p(stream), err,
+                             C.c_int32(len(err)))
+    if rc != 0:
+        raise BcuError(f"bcu_topk_static failed ({rc}): {err.value.decode()}")
+
+
 def _p(a, t):
     return a.ctypes.data_as(C.POINTER(t))
 

@@ -127,6 +127,21 @@ int bcu_fetch_results(bcu_engine* e, int64_t offset, int64_t n, const bcu_result
 /* ---- block-level top-k on (cost, candidate id) among VALID candidates of the last launch ------------
  * out_cost/out_id [k] ascending; *out_count = number of valid entries written (<= k). */
 int bcu_topk(bcu_engine* e, int32_t k, uint64_t* out_cost, uint64_t* out_id, int32_t* out_count);
+/* ---- the same selection without any allocation ------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Engine-free: the caller passes DEVICE
+ * pointers on the current device -- d_cost [n] u64 and d_flags [n] u32 (BCU_F_VALID marks a candidate that takes part)
+ * in, d_out_cost [k] / d_out_id [k] ascending by (cost, id) and padded with ~0, *d_out_count = number of valid candidates
+ * (may exceed k) out -- and the stream (a cudaStream_t; NULL = the default stream).  ids are first_candidate + index.
+ * Kernels are queued on the stream; the call does not synchronise and calls no cudaMalloc / cudaFree or any allocating
+ * routine.  The scratch of the selection (2 687 232 bytes) is a file-scope __device__ array that every GPU which loads the
+ * library holds until exit, which is why sizes are limited: n <= BCU_TOPK_STATIC_MAX_CANDIDATES, k <= BCU_TOPK_STATIC_MAX_K;
+ * anything larger is refused with BCU_ERR_INVALID and a message in err (optional, err_cap bytes).  All calls on a device
+ * share that array: calls ordered on one stream are fine, calls that overlap on the GPU race. */
+#define BCU_TOPK_STATIC_MAX_CANDIDATES ((int64_t)1 << 22)
+#define BCU_TOPK_STATIC_MAX_K 1024
+int bcu_topk_static(const uint64_t* d_cost, const uint32_t* d_flags, int64_t n, int64_t first_candidate, int32_t k,
+                    uint64_t* d_out_cost, uint64_t* d_out_id, int32_t* d_out_count, void* stream, char* err, int32_t err_cap);
 /* Final positions / potted mask of selected candidates of the last launch (ids are global ids). */
 int bcu_gather(bcu_engine* e, int32_t n, const uint64_t* ids, float* out_pos, uint32_t* out_potted, float* out_time);
 
