@@ -230,27 +230,108 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 // ---------------------------------------------------------------------------------------------------------------------
 // quartic: one thread per job.
 // ---------------------------------------------------------------------------------------------------------------------
+// -DQUARTIC_SORT_JOBS=1: AN EXPERIMENT THAT IS KEPT, NOT THE DEFAULT.  Measured (profiles/r02_ab_experiments.txt): 3.5 % SLOWER on
+// a large launch (95.4 against 98.9 M strikes/s) and 3 % slower on the 65 536-strike level -- the cost of the classification and
+// of the exchange, with no visible gain from the warps it makes uniform: the divergence that ncu shows inside the solver (16-20
+// of 32 lanes in the complex square roots, the divisions and atan2) is mostly between jobs of the SAME class (quadrant and
+// magnitude branches of the libm restatement), which no cheap key predicts.
+#ifndef QUARTIC_SORT_JOBS
+#define QUARTIC_SORT_JOBS 0
+#endif
+// Which arm of the solver a job will take: std::pow(complex, double) is a real pow() when its base is a positive real and
+// clog + exp + sincos otherwise (c_pow_real), and everything downstream (csqrt of real against complex values, the complex
+// divisions) follows that split -- two long, disjoint instruction streams that a warp with jobs of both kinds runs one after
+// the other.  The base is (deltaOne + sqrt(deltaOne^2 - 4 deltaZero^3)) / 2 of solve_quartic_roots, a few operations on the
+// coefficients.  A scheduling hint only: computed in plain double (no libm restatement); a wrong guess near a boundary costs
+// divergence and nothing else.
+__device__ __forceinline__ int quartic_job_class(const float co[5]) {
+    const double a = co[0], b = co[1], c = co[2], d = co[3], e = co[4];
+    const double dz = (c * c) - (3 * b * d) + (12 * a * e);
+    const double d1 = (2 * c * c * c) - (9 * b * c * d) + (27 * b * b * e) + (27 * a * d * d) - (72 * a * c * e);
+    const double R = d1 * d1 - 4.0 * dz * dz * dz;
+    if (!(R >= 0.0)) return 1;                 // complex base (three distinct real roots of the resolvent cubic)
+    return d1 + sqrt(R) > 0.0 ? 0 : 2;         // positive real base : negative real base
+}
+__device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsigned long long* key, const float co[5], uint32_t c2) {
+    float t;
+    if (collision_time_from_coefficients(co, &t)) {
+        const uint32_t ent = (c2 & ~JOB_MARK) >> 6;
+        if (c2 & JOB_MARK) {
+            // audit (pruneMode 2): the reach bound would have skipped this job, so its time must lose against the
+            // strike's best so far (which only decreases); anything else is a failure of the bound
+            const float tNow = from_ordered_bits((uint32_t)(__ldcg(key + (ent >> 5)) >> 32));
+            if (!(t > tNow)) atomicAdd(&w.counts[4 * ROUNDS + 2], 1u);
+        }
+        offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
+    }
+}
 __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb) {
     const uint32_t posted = w.counts[4 * round + 2];
     const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
     unsigned long long* key = w.key + (w.fused ? (size_t)0 : (size_t)(round % 3) * w.n);
+#if QUARTIC_SORT_JOBS
+    // The jobs of a tile change hands before they are solved: the CTA partitions its 128 jobs by class through shared memory,
+    // so that at most two of its four warps hold jobs of more than one class.  A job is its five coefficients and its code, and
+    // its result goes to the strike's key with an atomicMin, so it does not matter which thread solves it.
+    constexpr int NCLS = 3, NW = QUARTIC_BLOCK / 32;
+    __shared__ float sCo[5][QUARTIC_BLOCK];
+    __shared__ uint32_t sCode[QUARTIC_BLOCK];
+    __shared__ uint32_t sCnt[NW][NCLS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint64_t base = (uint64_t)bid * QUARTIC_BLOCK; base < nJobs; base += (uint64_t)nb * QUARTIC_BLOCK) {
+        const uint64_t j = base + threadIdx.x;
+        const bool have = j < nJobs;
+        float co[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        uint32_t c2 = 0;
+        int cls = -1;
+        if (have) {
+            #pragma unroll
+            for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
+            c2 = w.jobCode[j];
+            cls = quartic_job_class(co);
+        }
+        uint32_t mine = 0, cnt[NCLS];
+        #pragma unroll
+        for (int k = 0; k < NCLS; ++k) {
+            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
+            cnt[k] = __popc(m);
+            if (cls == k) mine = m;
+        }
+        if (lane < NCLS) sCnt[warp][lane] = lane == 0 ? cnt[0] : lane == 1 ? cnt[1] : cnt[2];
+        __syncthreads();
+        uint32_t at = __popc(mine & ((1u << lane) - 1u)), total = 0;
+        #pragma unroll
+        for (int k = 0; k < NCLS; ++k) {
+            #pragma unroll
+            for (int v = 0; v < NW; ++v) {
+                const uint32_t c = sCnt[v][k];
+                total += c;
+                if (k < cls || (k == cls && v < warp)) at += c;
+            }
+        }
+        if (have) {
+            #pragma unroll
+            for (int q = 0; q < 5; ++q) sCo[q][at] = co[q];
+            sCode[at] = c2;
+        }
+        __syncthreads();
+        const bool work = threadIdx.x < total;
+        if (work) {
+            #pragma unroll
+            for (int q = 0; q < 5; ++q) co[q] = sCo[q][threadIdx.x];
+            c2 = sCode[threadIdx.x];
+        }
+        __syncthreads();   // the tile is in registers: the next trip may overwrite it
+        if (work) quartic_solve_job(w, key, co, c2);
+    }
+#else
     for (uint64_t j = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)nb * QUARTIC_BLOCK) {
         float co[5];
         #pragma unroll
         for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
-        const uint32_t c2 = w.jobCode[j];
-        float t;
-        if (collision_time_from_coefficients(co, &t)) {
-            const uint32_t ent = (c2 & ~JOB_MARK) >> 6;
-            if (c2 & JOB_MARK) {
-                // audit (pruneMode 2): the reach bound would have skipped this job, so its time must lose against the
-                // strike's best so far (which only decreases); anything else is a failure of the bound
-                const float tNow = from_ordered_bits((uint32_t)(__ldcg(key + (ent >> 5)) >> 32));
-                if (!(t > tNow)) atomicAdd(&w.counts[4 * ROUNDS + 2], 1u);
-            }
-            offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
-        }
+        quartic_solve_job(w, key, co, w.jobCode[j]);
     }
+#endif
 }
 
 __global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
