@@ -127,10 +127,28 @@ constexpr uint32_t JOB_MARK = 0x80000000u;
 #endif
 constexpr int PARTNER_BATCH = PARTNER_BATCH_V;   // resting partners loaded per memory round trip (22 balls: two trips)   // audit: the bound would have skipped this job
 
+#ifndef JOB_SPLIT
+#define JOB_SPLIT 1
+#endif
+// Which arm of the closed-form solver a job will take, read off its coefficients: std::pow(complex, double) on the base
+// (deltaOne + sqrt(deltaOne^2 - 4 deltaZero^3)) / 2 (solve_quartic_roots) is a real pow() when that base is a positive real --
+// R = deltaOne^2 - 4 deltaZero^3 >= 0 and deltaOne + sqrt(R) > 0, i.e. deltaOne > 0 or deltaZero < 0 -- and clog + exp + sincos
+// otherwise, and the complex square roots and divisions downstream follow the same split (real against complex values).
+// A scheduling hint only: evaluated in plain double, and a wrong guess next to a boundary costs divergence, nothing else.
+__device__ __forceinline__ bool job_class_real(const float co[5]) {
+    const double a = co[0], b = co[1], c = co[2], d = co[3], e = co[4];
+    const double dz = (c * c) - (3.0 * b * d) + (12.0 * a * e);
+    const double d1 = (2.0 * c * c * c) - (9.0 * b * c * d) + (27.0 * b * b * e) + (27.0 * a * d * d) - (72.0 * a * c * e);
+    const double R = d1 * d1 - 4.0 * dz * dz * dz;
+    return R >= 0.0 && (d1 > 0.0 || dz < 0.0);
+}
+
 // shared memory of the items stage (one instance per CTA)
 struct ItemShared {
     ItemCounts cnt;
     uint32_t jobBase;
+    uint32_t splitBase[2][2];                    // JOB_SPLIT: [trip parity][class] first slot of this trip's jobs of a class
+    uint32_t splitCnt[2][ITEM_BLOCK / 32][2];    // JOB_SPLIT: [trip parity][warp][class] jobs of a class in a warp
     uint32_t ent[ITEM_BLOCK];
     float T[ITEM_BLOCK];
     RailGeom rails[MAX_RAILS];
@@ -419,6 +437,62 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
         __syncthreads();
 
         // ---- stage 2: quantised coefficients of the surviving pairs, one per thread -> global job queue -------------------
+#if JOB_SPLIT
+        // The queue is filled from both ends, by the arm of the solver a job will take (job_class_real): "real" jobs from slot
+        // 0 upwards (counts[4 round + 2]), "complex" jobs from the last slot downwards (counts[4 round + 3]), so that the warps
+        // of quartic_kernel -- 32 consecutive slots each -- hold jobs of ONE class (all but one warp of the grid).
+        {
+            const int cQ = cnt.pairs;
+            int trip = 0;
+            for (int iq0 = 0; iq0 < cQ; iq0 += ITEM_BLOCK, ++trip) {   // block-uniform
+                const int iq = iq0 + tid, par = trip & 1;
+                const bool have = iq < cQ;
+                float co[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+                uint32_t jc = 0;
+                bool real = false;
+                if (have) {
+                    const uint32_t c2 = qPairs[iq];
+                    const uint32_t en = sEnt[(c2 >> 6) & (ITEM_BLOCK - 1)];
+                    const int o = (int)(c2 & 31u), b = (int)(en & 31u);
+                    const int64_t s = en >> 5, g1 = (int64_t)b * n + s, g2 = (int64_t)o * n + s;
+                    const bool partnerDynamic = (c2 & 32u) != 0;   // a resting partner is position only (rest_ball(), bcu_pipeline.cu)
+                    const float2 x1 = w.pos[g1], y1 = w.vel[g1], z1 = w.acc[g1], x2 = w.pos[g2];
+                    float2 y2 = make_float2(0.f, 0.f), z2 = make_float2(0.f, 0.f);
+                    if (partnerDynamic) { y2 = w.vel[g2]; z2 = w.acc[g2]; }
+                    const v2 a2 = partnerDynamic ? mk(z2.x, z2.y) : rest_acc(p_phys);
+                    collision_coefficients(mk(z1.x, z1.y), mk(y1.x, y1.y), mk(x1.x, x1.y), a2, mk(y2.x, y2.y),
+                                           mk(x2.x, x2.y), diameter, co);
+                    jc = (en << 6) | (c2 & 63u) | ((c2 & 0x8000u) ? JOB_MARK : 0u);
+                    real = job_class_real(co);
+                }
+                const unsigned mR = __ballot_sync(FULL, have && real), mC = __ballot_sync(FULL, have && !real);
+                if (lane == 0) { sh.splitCnt[par][tid >> 5][0] = __popc(mR); sh.splitCnt[par][tid >> 5][1] = __popc(mC); }
+                __syncthreads();
+                if (tid == 0) {
+                    uint32_t tR = 0, tC = 0;
+                    #pragma unroll
+                    for (int v = 0; v < ITEM_BLOCK / 32; ++v) { tR += sh.splitCnt[par][v][0]; tC += sh.splitCnt[par][v][1]; }
+                    if (tR) sh.splitBase[par][0] = atomicAdd(jobCount, tR);
+                    if (tC) sh.splitBase[par][1] = atomicAdd(jobCount + 1, tC);
+                }
+                __syncthreads();
+                if (have) {
+                    const int k = real ? 0 : 1;
+                    uint32_t at = sh.splitBase[par][k] + __popc((real ? mR : mC) & ((1u << lane) - 1u));
+                    #pragma unroll
+                    for (int v = 0; v < ITEM_BLOCK / 32; ++v) at += v < (tid >> 5) ? sh.splitCnt[par][v][k] : 0u;
+                    if (at < w.jobCap) {
+                        const uint64_t j = real ? (uint64_t)at : (uint64_t)w.jobCap - 1u - at;
+                        #pragma unroll
+                        for (int q = 0; q < 5; ++q) w.jobCo[(size_t)q * w.jobCap + j] = co[q];
+                        w.jobCode[j] = jc;
+                    } else {
+                        w.counts[4 * ROUNDS + 3] = 1u;  // queue overflow: the host grows the queue and re-runs the launch
+                    }
+                }
+            }
+        }
+#else
         {
             const int cQ = cnt.pairs;
             if (tid == 0 && cQ > 0) sJobBase = atomicAdd(jobCount, (uint32_t)cQ);   // one global atomic per tile
@@ -446,6 +520,7 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                 }
             }
         }
+#endif
         __syncthreads();
     }
     if (p.out.counters && skipped) atomicAdd(&p.out.counters[5], skipped);

@@ -231,10 +231,9 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 // quartic: one thread per job.
 // ---------------------------------------------------------------------------------------------------------------------
 // -DQUARTIC_SORT_JOBS=1: AN EXPERIMENT THAT IS KEPT, NOT THE DEFAULT.  Measured (profiles/r02_ab_experiments.txt): 3.5 % SLOWER on
-// a large launch (95.4 against 98.9 M strikes/s) and 3 % slower on the 65 536-strike level -- the cost of the classification and
-// of the exchange, with no visible gain from the warps it makes uniform: the divergence that ncu shows inside the solver (16-20
-// of 32 lanes in the complex square roots, the divisions and atan2) is mostly between jobs of the SAME class (quadrant and
-// magnitude branches of the libm restatement), which no cheap key predicts.
+// a large launch (95.4 against 98.9 M strikes/s) and 3 % slower on the 65 536-strike level -- the classification and the exchange
+// are paid per job and two of a CTA's four warps stay mixed.  The same idea on the PRODUCER's side won: items_kernel fills the
+// queue from both ends by class (JOB_SPLIT, bcu_items.cuh), which costs the consumer nothing.
 #ifndef QUARTIC_SORT_JOBS
 #define QUARTIC_SORT_JOBS 0
 #endif
@@ -266,8 +265,13 @@ __device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsign
     }
 }
 __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb) {
-    const uint32_t posted = w.counts[4 * round + 2];
-    const uint64_t nJobs = posted < w.jobCap ? posted : w.jobCap;
+    // the queue is filled from both ends (bcu_items.cuh stage 2): nFront jobs from slot 0 upwards, nBack from the last slot downwards
+    const uint32_t postedFront = w.counts[4 * round + 2], postedBack = w.counts[4 * round + 3];
+    const uint64_t nFront = postedFront < w.jobCap ? postedFront : w.jobCap;
+    const uint64_t nBack = postedBack < w.jobCap - nFront ? postedBack : w.jobCap - nFront;
+    const uint64_t nJobs = nFront + nBack;
+    if ((uint64_t)postedFront + postedBack > w.jobCap && bid == 0 && threadIdx.x == 0)
+        w.counts[4 * ROUNDS + 3] = 1u;   // the two ends met: the host grows the queue and re-runs the launch
     unsigned long long* key = w.key + (w.fused ? (size_t)0 : (size_t)(round % 3) * w.n);
 #if QUARTIC_SORT_JOBS
     // The jobs of a tile change hands before they are solved: the CTA partitions its 128 jobs by class through shared memory,
@@ -279,8 +283,9 @@ __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, 
     __shared__ uint32_t sCnt[NW][NCLS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (uint64_t base = (uint64_t)bid * QUARTIC_BLOCK; base < nJobs; base += (uint64_t)nb * QUARTIC_BLOCK) {
-        const uint64_t j = base + threadIdx.x;
-        const bool have = j < nJobs;
+        const uint64_t v = base + threadIdx.x;
+        const bool have = v < nJobs;
+        const uint64_t j = v < nFront ? v : w.jobCap - 1u - (v - nFront);
         float co[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
         uint32_t c2 = 0;
         int cls = -1;
@@ -325,7 +330,8 @@ __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, 
         if (work) quartic_solve_job(w, key, co, c2);
     }
 #else
-    for (uint64_t j = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; j < nJobs; j += (uint64_t)nb * QUARTIC_BLOCK) {
+    for (uint64_t v = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; v < nJobs; v += (uint64_t)nb * QUARTIC_BLOCK) {
+        const uint64_t j = v < nFront ? v : w.jobCap - 1u - (v - nFront);
         float co[5];
         #pragma unroll
         for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
@@ -629,6 +635,7 @@ __global__ void counters_kernel(const LaunchParams* __restrict__ pp, PipeWorkspa
         if (w.counts[4 * r + 0] == 0) continue;
         pairs += d * p.states.nBalls; rails += d * p.table->nRails; pockets += d * p.table->nPockets;
         quartics += w.counts[4 * r + 2];
+        quartics += w.counts[4 * r + 3];   // the queue's other end
     }
     atomicAdd(&p.out.counters[1], pairs); atomicAdd(&p.out.counters[2], quartics);
     atomicAdd(&p.out.counters[3], rails); atomicAdd(&p.out.counters[4], pockets);
@@ -835,7 +842,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         fprintf(stderr, "[bcu timing] init %.1f us\n", ms(0));
         for (int r = 0; r < ROUNDS; ++r) {
             fprintf(stderr, "[bcu timing] round %2d live %7u dyn %7u jobs %7u : items %6.1f quartic %6.1f apply %6.1f us\n", r,
-                    counts[4 * r], counts[4 * r + 1], counts[4 * r + 2], ms(1 + 3 * r), ms(2 + 3 * r), ms(3 + 3 * r));
+                    counts[4 * r], counts[4 * r + 1], counts[4 * r + 2] + counts[4 * r + 3], ms(1 + 3 * r), ms(2 + 3 * r), ms(3 + 3 * r));
             for (int k = 0; k < 3; ++k) sum[k] += ms(1 + 3 * r + k);
         }
         float tot = 0; cudaEventElapsedTime(&tot, ev.front(), ev.back());
