@@ -237,6 +237,9 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 #ifndef QUARTIC_SORT_JOBS
 #define QUARTIC_SORT_JOBS 0
 #endif
+#ifndef QUARTIC_REAL_EIGHTHS
+#define QUARTIC_REAL_EIGHTHS 4
+#endif
 // Which arm of the solver a job will take: std::pow(complex, double) is a real pow() when its base is a positive real and
 // clog + exp + sincos otherwise (c_pow_real), and everything downstream (csqrt of real against complex values, the complex
 // divisions) follows that split -- two long, disjoint instruction streams that a warp with jobs of both kinds runs one after
@@ -264,7 +267,9 @@ __device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsign
         offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
     }
 }
-__device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb) {
+template <bool SM_CLASS>
+__device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb, int pref, uint32_t ticket0) {
+    (void)pref; (void)ticket0; (void)nb;
     // the queue is filled from both ends (bcu_items.cuh stage 2): nFront jobs from slot 0 upwards, nBack from the last slot downwards
     const uint32_t postedFront = w.counts[4 * round + 2], postedBack = w.counts[4 * round + 3];
     const uint64_t nFront = postedFront < w.jobCap ? postedFront : w.jobCap;
@@ -330,6 +335,48 @@ __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, 
         if (work) quartic_solve_job(w, key, co, c2);
     }
 #else
+  if constexpr (SM_CLASS) {
+    // Every SM works on ONE class of jobs for as long as there are any: the solver's two arms are disjoint instruction streams
+    // (17 KB and 30 KB of the 39 KB a mixed SM walks through), the SM's instruction cache holds 32 KB, and with both classes
+    // resident quartic_kernel was bound by instruction fetch (sm__icc hit rate 73 %, `no instruction` the largest stall,
+    // profiles/r02_quartic_dense_big_round_ncu_full.txt).  A CTA prefers the class of its SM (preferredClass: by %smid), takes
+    // tiles of 128 jobs of that class by ticket -- its first ticket was drawn before the grid dependency, the next one is
+    // drawn before the current tile is solved, so the atomics' latency is never waited for -- and moves to the other class
+    // once its own is used up.
+    __shared__ uint32_t sNext;
+    const uint64_t nOf[2] = {nFront, nBack};
+    uint32_t* tickets = w.tickets + 2 * round;
+    int cls = pref;
+    uint32_t t = ticket0;
+    bool moved = false;
+    for (;;) {
+        if ((uint64_t)t * QUARTIC_BLOCK >= nOf[cls]) {
+            if (moved) break;
+            moved = true;
+            cls ^= 1;
+            if (nOf[cls] == 0) break;
+            __syncthreads();
+            if (threadIdx.x == 0) sNext = atomicAdd(&tickets[cls], 1u);
+            __syncthreads();
+            t = sNext;
+            continue;
+        }
+        uint32_t nxt = 0;
+        if (threadIdx.x == 0) nxt = atomicAdd(&tickets[cls], 1u);   // used after the solve
+        const uint64_t v = (uint64_t)t * QUARTIC_BLOCK + threadIdx.x;
+        if (v < nOf[cls]) {
+            const uint64_t j = cls == 0 ? v : w.jobCap - 1u - v;
+            float co[5];
+            #pragma unroll
+            for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
+            quartic_solve_job(w, key, co, w.jobCode[j]);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) sNext = nxt;
+        __syncthreads();
+        t = sNext;
+    }
+  } else {
     for (uint64_t v = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; v < nJobs; v += (uint64_t)nb * QUARTIC_BLOCK) {
         const uint64_t j = v < nFront ? v : w.jobCap - 1u - (v - nFront);
         float co[5];
@@ -337,18 +384,45 @@ __device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, 
         for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
         quartic_solve_job(w, key, co, w.jobCode[j]);
     }
+  }
 #endif
 }
 
-__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    cudaGridDependencySynchronize();
-    quartic_body(w, round, blockIdx.x, gridDim.x);
+// class an SM prefers: QUARTIC_REAL_EIGHTHS of every 8 SMs take the "real" jobs (front of the queue), the others the "complex" ones
+__device__ __forceinline__ int preferredClass() {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    return (smid & 7u) < (unsigned)QUARTIC_REAL_EIGHTHS ? 0 : 1;
 }
+template <bool SM_CLASS>
+__device__ __forceinline__ void quartic_entry(const PipeWorkspace& w, int round) {
+    if constexpr (SM_CLASS && !QUARTIC_SORT_JOBS) {
+        __shared__ uint32_t sFirst;
+        const int pref = preferredClass();
+        // the tickets are zeroed at the start of the launch and belong to this round's quartic kernel alone: nothing the
+        // previous kernel writes is read before the grid dependency
+        if (threadIdx.x == 0) sFirst = atomicAdd(&w.tickets[2 * round + pref], 1u);
+        if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+        cudaGridDependencySynchronize();
+        __syncthreads();
+        quartic_body<true>(w, round, blockIdx.x, gridDim.x, pref, sFirst);
+    } else {
+        if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+        cudaGridDependencySynchronize();
+        quartic_body<false>(w, round, blockIdx.x, gridDim.x, 0, 0u);
+    }
+}
+// Three instantiations (launch_pipeline chooses by the size of the part): the default one, the one compiled for more resident
+// CTAs per SM, and that one with the per-SM job classes.  Measured (profiles/r02_ab_experiments.txt): the tickets pay only on the
+// largest parts -- 1000 tables x 4096 strikes (parts of 2^20) 107.6 against 105.6 M strikes/s, 74.6 against 71.6 M exact; parts
+// of 2^19 the same either way; parts of 2^16 .. 2^18 LOSE 5-17 %, and the 65 536-strike level loses 8-10 % (its rounds are
+// latency-bound: a barrier per tile and, when a CTA changes class, an atomic round trip that is waited for).
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) { quartic_entry<false>(w, round); }
 __global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_DENSE_MIN_BLOCKS) quartic_kernel_dense(PipeWorkspace w, int round) {
-    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-    cudaGridDependencySynchronize();
-    quartic_body(w, round, blockIdx.x, gridDim.x);
+    quartic_entry<false>(w, round);
+}
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_DENSE_MIN_BLOCKS) quartic_kernel_dense_smc(PipeWorkspace w, int round) {
+    quartic_entry<true>(w, round);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -674,7 +748,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     const size_t oStop = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oLive = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oDyn = take((size_t)2 * w.dynCap * sizeof(uint32_t));
-    const size_t oCounts = take((size_t)4 * (ROUNDS + 1) * sizeof(uint32_t));
+    const size_t oCounts = take((size_t)(2 + 4) * (ROUNDS + 1) * sizeof(uint32_t));   // tickets [rounds + 1][2], then counts
     const size_t oCo = take((size_t)5 * w.jobCap * sizeof(float)), oCode = take(w.jobCap * sizeof(uint32_t));
     if (layout) {
         unsigned char* b = reinterpret_cast<unsigned char*>(layout->base);
@@ -685,7 +759,8 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
         w.key = reinterpret_cast<unsigned long long*>(b + oKey); w.T = reinterpret_cast<float*>(b + oT);
         w.dynMask = reinterpret_cast<uint32_t*>(b + oDm); w.restMask = reinterpret_cast<uint32_t*>(b + oRm);
         w.live = reinterpret_cast<uint32_t*>(b + oLive); w.dyn = reinterpret_cast<uint32_t*>(b + oDyn);
-        w.counts = reinterpret_cast<uint32_t*>(b + oCounts);
+        w.tickets = reinterpret_cast<uint32_t*>(b + oCounts);
+        w.counts = w.tickets + 2 * (ROUNDS + 1);
         w.jobCo = reinterpret_cast<float*>(b + oCo); w.jobCode = reinterpret_cast<uint32_t*>(b + oCode);
         w.buf[0] = StateBuf{w.pos, w.vel, w.vn, w.acc, w.nextRolling, w.meta};
         w.buf[1] = StateBuf{reinterpret_cast<float2*>(b + oPos2), reinterpret_cast<float2*>(b + oVel2), reinterpret_cast<float2*>(b + oVn2),
@@ -712,7 +787,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
     const size_t countWords = (size_t)4 * (ROUNDS + 1) - (resetOverflow ? 0 : 1);
-    if ((e = cudaMemsetAsync(w.counts, 0, countWords * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(w.tickets, 0, ((size_t)2 * (ROUNDS + 1) + countWords) * sizeof(uint32_t), stream)) != cudaSuccess) return e;   // tickets + counts
     const size_t itemSmem = (size_t)ITEM_BLOCK * (2 * nBalls) * sizeof(uint16_t);
     (void)nRails; (void)nPockets;
     const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
@@ -801,12 +876,13 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // of 2^20) 99.1 M strikes/s against 93.7 M, parts of 131 072: 96.7 against 91.3; parts of 65 536: -1 % with the reach bound,
     // +6 % without; parts of 32 768 (the 65 536-strike level, latency-bound rounds) lose 3-5 % with them.  Same code, same results.
     const bool denseI = w.n >= cfg.denseMinItems, denseQ = w.n >= cfg.denseMinQuartic;
+    const bool smClass = denseQ && w.n >= cfg.smClassMin;   // quartic_kernel_dense_smc: every SM works on one class of jobs
     for (int r = 0; r < ROUNDS && !w.fused && !w.merged; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * (denseI ? cfg.occItemsDense : occItems), ITEM_BLOCK, itemSmem);
         if ((e = cudaLaunchKernelEx(&ci, denseI ? items_kernel_dense : items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
         cudaLaunchConfig_t cq = cfgOf(sms * (denseQ ? cfg.occQuarticDense : occQuartic), QUARTIC_BLOCK, 0);
-        if ((e = cudaLaunchKernelEx(&cq, denseQ ? quartic_kernel_dense : quartic_kernel, w, r)) != cudaSuccess) return e;
+        if ((e = cudaLaunchKernelEx(&cq, smClass ? quartic_kernel_dense_smc : denseQ ? quartic_kernel_dense : quartic_kernel, w, r)) != cudaSuccess) return e;
         mark();
         cudaLaunchConfig_t ca = cfgOf(sms * occApply, APPLY_BLOCK, 0);
         if ((e = cudaLaunchKernelEx(&ca, apply_kernel, p, w, r)) != cudaSuccess) return e;
