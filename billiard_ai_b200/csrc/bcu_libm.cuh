@@ -55,11 +55,24 @@ BCU_HD double u2d(uint64_t u) {
 // n / d.  The device's IEEE division leaves its inline fast path for a ~100-instruction subroutine whenever the quotient is
 // zero or subnormal, and this solver divides exact zeros all the time (real inputs carried as complex numbers with a zero
 // imaginary part).  0 / d for a non-zero, non-NaN d is a zero with the XOR of the signs -- returned directly.
+// -DBCU_OUTLINE_DIVSQRT=1: ONE out-of-line copy of the IEEE division and of the square root per kernel instead of an inline
+// expansion (~20 instructions and a slow-path call) at each of their ~18 sites in the solver -- quartic_kernel is bound by
+// instruction fetch, and these expansions are 5 KB of the 39 KB a job walks through.  Same operations, same results.
+#ifndef BCU_OUTLINE_DIVSQRT
+#define BCU_OUTLINE_DIVSQRT 0
+#endif
+#if defined(__CUDA_ARCH__) && BCU_OUTLINE_DIVSQRT
+BCU_HD_NOINLINE double bcu_div_raw(double n, double d) { return n / d; }
+BCU_HD_NOINLINE double bcu_sqrt(double x) { return sqrt(x); }
+#else
+BCU_HD double bcu_div_raw(double n, double d) { return n / d; }
+BCU_HD double bcu_sqrt(double x) { return sqrt(x); }
+#endif
 BCU_HD double bcu_div(double n, double d) {
 #if defined(__CUDA_ARCH__)
     if (n == 0.0 && d == d && d != 0.0) return u2d((d2u(n) ^ d2u(d)) & 0x8000000000000000ull);
 #endif
-    return n / d;
+    return bcu_div_raw(n, d);
 }
 
 // ---- tables -------------------------------------------------------------------------------------------------
@@ -375,7 +388,7 @@ BCU_HD double g_log1p(double x) {
             hu = (int32_t)(d2u(u) >> 32);
             k = (hu >> 20) - 1023;
             c = (k > 0) ? 1.0 - (u - x) : x - (u - 1.0);
-            c = c / u;
+            c = bcu_div_raw(c, u);
         } else {
             u = x;
             hu = (int32_t)(d2u(u) >> 32);
@@ -405,7 +418,7 @@ BCU_HD double g_log1p(double x) {
         c = bcu_fma(kd, ln2_lo, c);
         return bcu_fma(kd, ln2_hi, -((R0 - c) - f));         // k*ln2_hi - ((R - (k*ln2_lo + c)) - f)
     }
-    const double s = f / (2.0 + f);
+    const double s = bcu_div_raw(f, 2.0 + f);
     const double zz = s * s;
     // R = z*Lp1 + z2*(Lp2 + z*Lp3) + z4*(Lp4 + z*Lp5) + z6*(Lp6 + z*Lp7), glibc's pairing
     const double R2 = bcu_fma(Lp3, zz, Lp2);
@@ -547,8 +560,8 @@ BCU_HD double g_atan2(double y, double x) {
     // u = min/max, du = its correction: one stream for both orders (operands selected)
     const bool yLess = ay < ax;
     const double num = yLess ? ay : ax, den = yLess ? ax : ay;
-    const double u = num / den;
-    const double du = ((num - u * den) - bcu_fma(u, den, -(u * den))) / den;
+    const double u = bcu_div_raw(num, den);
+    const double du = bcu_div_raw((num - u * den) - bcu_fma(u, den, -(u * den)), den);
     double z;
     if (x > 0 && yLess) {                                 // (i) atan(ay/ax)
         if (u < inv16) {

@@ -100,7 +100,7 @@ BCU_HD double g_hypot(double x, double y) {
     } else if (ax * EPS >= ay) {
         return ax + ay;
     }
-    double h = sqrt(ax * ax + ay * ay);
+    double h = bcu_sqrt(ax * ax + ay * ay);
     // both correction formulas are evaluated and one is selected (no divergent branch; identical operations)
     const bool small = h <= 2.0 * ay;
     const double delta = h - (small ? ay : ax);
@@ -120,17 +120,17 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
     if (x.im == 0.0) {
         if (x.re < 0) {
             res.re = 0;
-            res.im = copysign(sqrt(-x.re), x.im);
+            res.im = copysign(bcu_sqrt(-x.re), x.im);
         } else {
-            res.re = fabs(sqrt(x.re));
+            res.re = fabs(bcu_sqrt(x.re));
             res.im = copysign(0.0, x.im);
         }
         return res;
     }
     if (x.re == 0.0) {
         double r;
-        if (fabs(x.im) >= 2 * DMIN) r = sqrt(0.5 * fabs(x.im));
-        else r = 0.5 * sqrt(2 * fabs(x.im));
+        if (fabs(x.im) >= 2 * DMIN) r = bcu_sqrt(0.5 * fabs(x.im));
+        else r = 0.5 * bcu_sqrt(2 * fabs(x.im));
         res.re = r;
         res.im = copysign(r, x.im);
         return res;
@@ -153,7 +153,7 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
         // re > 0:  r = sqrt(0.5 (d + re)), s = 0.5 (im / r);   re < 0:  s = sqrt(0.5 (d - re)), r = |0.5 (im / s)|.
         // d - re with re < 0 is d + |re|, so both arms are  t = sqrt(0.5 (d + |re|)), u = 0.5 (im / t)  with roles swapped.
         const bool pos = x.re > 0;
-        double t = sqrt(0.5 * (d + fabs(x.re))), u;
+        double t = bcu_sqrt(0.5 * (d + fabs(x.re))), u;
         if (scale == 1 && fabs(x.im) < 1) { u = bcu_div(x.im, t); t = t * 2.0; scale = 0; }
         else u = 0.5 * bcu_div(x.im, t);
         r = pos ? t : fabs(u);

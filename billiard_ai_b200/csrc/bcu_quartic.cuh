@@ -18,7 +18,7 @@ BCU_HD double quartic_discriminant(double a, double b, double c, double d, doubl
 
 // S of billiard_physics.cpp:500: 0.5 * sqrt(-(2/3) p + (1/(3a)) (Q + deltaZero/Q))
 BCU_HD cplx quartic_S(cplx p, cplx Q, cplx deltaZero, double a) {
-    cplx inner = c_add(c_scale(p, -(2.0 / 3.0)), c_scale(c_add(Q, c_div(deltaZero, Q)), (1.0 / (3.0 * a))));
+    cplx inner = c_add(c_scale(p, -(2.0 / 3.0)), c_scale(c_add(Q, c_div(deltaZero, Q)), bcu_div_raw(1.0, (3.0 * a))));
     return c_scale(c_sqrt(inner), 0.5);
 }
 
@@ -29,8 +29,8 @@ BCU_HD int solve_quartic_roots(double a, double b, double c, double d, double e,
 
     double b3, a3, c3;   // std::pow(b, 3.0), std::pow(a, 3.0), std::pow(c, 3.0) (:484-487)
     g_cubes3(b, a, c, &b3, &a3, &c3);
-    cplx p = c_make(((8 * a * c) - (3 * b * b)) / (8 * a * a));
-    cplx q = c_make((b3 - (4 * a * b * c) + (8 * a * a * d)) / (8 * a3));
+    cplx p = c_make(bcu_div_raw((8 * a * c) - (3 * b * b), (8 * a * a)));
+    cplx q = c_make(bcu_div_raw(b3 - (4 * a * b * c) + (8 * a * a * d), (8 * a3)));
     cplx deltaZero = c_make((c * c) - (3 * b * d) + (12 * a * e));
     cplx deltaOne = c_make((2 * c3) - (9 * b * c * d) + (27 * b * b * e) + (27 * a * d * d) - (72 * a * c * e));
 
@@ -63,7 +63,7 @@ BCU_HD int solve_quartic_roots(double a, double b, double c, double d, double e,
     cplx disc1 = c_add(shared1, shared2);
     cplx disc2 = c_sub(shared1, shared2);
 
-    cplx firstPartShared = c_make(-b / (4 * a));
+    cplx firstPartShared = c_make(bcu_div_raw(-b, (4 * a)));
     cplx first1 = c_sub(firstPartShared, S);
     cplx first2 = c_add(firstPartShared, S);
 
