@@ -234,21 +234,24 @@ __device__ __forceinline__ void items_body(ItemShared& sh, uint16_t* smemQ, cons
                     // per rail; here a rail is dropped only when the exact test is certain to fail: the intersection parameter
                     // t = N / detDV is negative by more than any rounding (N detDV < 0, |t| > 1e-10), or -- for lines at more than
                     // ~1.1 degrees (sin^2 >= 4e-4), where both this estimate and the reference's u are accurate to < 1e-2 -- the
-                    // crossing lies more than 5 % of the segment outside it.  Everything else is a candidate (prune mode 0: all).
+                    // crossing lies more than 5 % of the segment outside it (prune mode 0: the first test only).  Everything else is a candidate.
                     const float speedSq = dot(vel, vel);
                     for (int r = 0; r < R; ++r) {
                         const RailGeom rg = sRails[r];
                         const float detDV = vel.x * rg.dy - vel.y * rg.dx;
                         const float nT = (rg.dx * pos.y - rg.dy * pos.x) + sDetQV[r];
-                        bool cand = r != lastRail && detDV != 0.0f;
+                        // "behind" is exact, not an estimate -- nT and detDV are the very operands of the exact stage's division
+                        // lambda = nT / detDV, and a quotient of opposite signs and magnitude > 1e-10 is a negative float whatever
+                        // the rounding, which that stage rejects (lambda < 0) -- so it also holds with the filters off
+                        const bool behind = nT * detDV < 0.0f && fabsf(nT) > 1e-10f * fabsf(detDV);
+                        bool cand = r != lastRail && detDV != 0.0f && !behind;
                         if (prune) {
-                            const bool behind = nT * detDV < 0.0f && fabsf(nT) > 1e-10f * fabsf(detDV);
                             const float lenSq = sRailLenSq[r];
                             const float nU = (pos.x - rg.sx) * vel.y - (pos.y - rg.sy) * vel.x;   // u = nU / -detDV
                             const float den = -detDV, sgnU = den < 0.0f ? -nU : nU, aden = fabsf(den);
                             const bool wellCond = lenSq > 0.0f && detDV * detDV >= 4e-4f * (speedSq * lenSq);
                             const bool outside = wellCond && (sgnU < -0.05f * aden || sgnU > 1.05f * aden);
-                            cand = cand && !behind && !outside;
+                            cand = cand && !outside;
                         }
                         if (cand) railMask |= 1u << r;
                     }
