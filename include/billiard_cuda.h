@@ -338,7 +338,9 @@ int bcu_get_counters(bcu_engine* e, uint64_t* out5);
  * before the strike's best event time so far cannot produce the next event (the reference would solve its quartic,
  * billiard_physics.cpp:283-381, and discard the result in min(), billiard_search.cpp:2002-2013), so it is not solved.
  * mode 0 (DEFAULT): off -- every test the reference makes is made and every quartic it solves is solved; parity with the
- *         reference follows from construction.
+ *         reference follows from construction.  (One shortcut is taken in every mode because it is the reference's own test
+ *         read off before the division: a rail whose intersection parameter lambda = N / D has N and D of opposite signs
+ *         and |N| > 1e-10 |D| is rejected by `lambda < 0` whatever the rounding, so lambda is not computed for it.)
  * mode 1: on (opt-in, for throughput).  The bound is a theorem about the roots of the collision polynomial plus an
  *         EMPIRICAL characterisation of where the reference's closed-form solver returns them:
  *         audited on > 8e8 random strikes with no differing result, not proven.  Also enables the division-free rail /
