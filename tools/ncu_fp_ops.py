@@ -33,6 +33,7 @@ def main(path, counters_path, note):
     launches = collections.OrderedDict()
     for r in rows:
         name = re.sub(r"\(.*", "", r[ki]).replace("unnamed>::", "").split("::")[-1]
+        name = re.sub(r"_dense(_smc)?$", "", name)   # the instantiations for large parts: same code, other launch bounds
         v = float(r[vi].replace(",", ""))
         if r[ui] == "ns":
             v /= 1e3
