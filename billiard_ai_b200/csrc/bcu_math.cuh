@@ -118,13 +118,13 @@ BCU_HD_NOINLINE cplx g_csqrt(cplx x) {
     const double DMIN = 2.2250738585072014e-308, DMAX = 1.7976931348623157e308;
     cplx res;
     if (x.im == 0.0) {
-        if (x.re < 0) {
-            res.re = 0;
-            res.im = copysign(bcu_sqrt(-x.re), x.im);
-        } else {
-            res.re = fabs(bcu_sqrt(x.re));
-            res.im = copysign(0.0, x.im);
-        }
+        // re < 0: (0, copysign(sqrt(-re), im));  otherwise: (|sqrt(re)|, copysign(0, im)).  One square root of |re| serves both
+        // arms (|sqrt(-0)| = sqrt(0) = 0): the lanes of a warp take them about equally often (the two discriminants of a
+        // quartic with two real roots have opposite signs).
+        const double r = bcu_sqrt(fabs(x.re));
+        const bool neg = x.re < 0;
+        res.re = neg ? 0.0 : r;
+        res.im = copysign(neg ? r : 0.0, x.im);
         return res;
     }
     if (x.re == 0.0) {

@@ -592,3 +592,42 @@ def test_experimental_round_layouts_are_bit_identical(engine, table, layout):
     finally:
         engine.set_prune(0)
         other.close()
+
+
+@pytest.mark.parametrize("knobs", [{"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "1000000000"}, {"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "0"},
+                                   {"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "0", "BCU_JOBS_PER_STRIKE": "1"}],
+                         ids=["dense", "dense-sm-classes", "dense-sm-classes-queue-overflow"])
+def test_large_part_kernels_are_bit_identical(engine, table, knobs):
+    """launch_pipeline takes other instantiations of items / quartic for large parts (compiled for more resident CTAs per SM;
+    from 2^20 strikes on, every SM prefers one class of quartic jobs and takes tiles by ticket).  The thresholds are engine
+    settings read from the environment at bcu_create: an engine that uses those kernels on a SMALL launch must return exactly what
+    the default engine returns -- every output incl. the event log, both prune modes -- also when the two-ended job queue
+    overflows and the launch is repeated with a larger one."""
+    from billiard_ai_b200 import Engine, workloads as W
+    pos, types = W.snooker22_open(33)
+    dirs, speeds = W.grid(192, 24)
+    vx, vy = W.grid_velocities(dirs, speeds)
+    old = {k: os.environ.get(k) for k in knobs}
+    os.environ.update(knobs)
+    try:
+        other = Engine.from_table(table, SNOOKER_SCORES, cue_type=TYPE_CODE["WHITE"])
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    try:
+        for prune in (0, 1):
+            res = []
+            for e in (engine, other):
+                e.set_prune(prune)
+                e.set_states(pos, types, 1 << TYPE_CODE["RED"])
+                res.append(e.evaluate(0, vx, vy, 100000, 7, final_pos=True, event_log=True))
+            for key in ("cost", "flags_raw", "potted", "event_log"):
+                assert np.array_equal(res[0][key], res[1][key]), (knobs, prune, key)
+            assert np.array_equal(res[0]["final_time"].view(np.uint32), res[1]["final_time"].view(np.uint32))
+            assert np.array_equal(res[0]["final_pos"].view(np.uint32), res[1]["final_pos"].view(np.uint32))
+    finally:
+        engine.set_prune(0)
+        other.close()
