@@ -284,7 +284,6 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     if (const char* dv = getenv("BCU_DENSE_MIN")) { const long long v = atoll(dv); e->pipeCfg.denseMinItems = e->pipeCfg.denseMinQuartic = v < 0 ? 0 : v; }
     if (const char* dv = getenv("BCU_DENSE_MIN_ITEMS")) { const long long v = atoll(dv); e->pipeCfg.denseMinItems = v < 0 ? 0 : v; }
     if (const char* dv = getenv("BCU_DENSE_MIN_QUARTIC")) { const long long v = atoll(dv); e->pipeCfg.denseMinQuartic = v < 0 ? 0 : v; }
-    if (const char* dv = getenv("BCU_SM_CLASS_MIN")) { const long long v = atoll(dv); e->pipeCfg.smClassMin = v < 0 ? 0 : v; }
     if (const char* lv = getenv("BCU_LAYOUT")) { const int v = atoi(lv); e->pipeCfg.layout = v == 1 ? 1 : v == 2 ? 2 : 0; }
     if (const char* lv = getenv("BCU_STEP_LANES")) e->pipeCfg.stepLanes = atoi(lv);
     e->selectTiming = getenv("BCU_SELECT_TIMING") != nullptr;

@@ -88,7 +88,6 @@ struct PipeWorkspace {
     // stream-compacted lists, by round & 1
     uint32_t* live;            // [2][n] strike ids
     uint32_t* dyn;             // [2][dynCap] strike << 5 | ball
-    uint32_t* tickets;         // [rounds + 1][2] tile tickets of quartic_kernel per job class; directly in front of counts (one memset)
     uint32_t* counts;          // [rounds + 1][4] {live, dynamic balls, quartic jobs, -}; last row: {-, -, audit failures, queue overflow}
     // quartic jobs of the round
     float* jobCo;              // [5][jobCap]
@@ -116,11 +115,10 @@ struct PipeLaunchCfg {
     int occItems = 0, occQuartic = 0, occApply = 0;
     size_t occSmem = ~(size_t)0;
     int occStep = 0;
-    int occItemsDense = 0, occQuarticDense = 0;
-    // parts of this many strikes and more run items_kernel_dense / quartic_kernel_dense (BCU_DENSE_MIN sets both,
+    int occItemsDense = 0, occQuarticWide = 0;
+    // parts of this many strikes and more run items_kernel_dense / quartic_kernel_wide (BCU_DENSE_MIN sets both,
     // BCU_DENSE_MIN_ITEMS / BCU_DENSE_MIN_QUARTIC one of them)
     int64_t denseMinItems = 65536, denseMinQuartic = 65536;
-    int64_t smClassMin = 1 << 20;   // BCU_SM_CLASS_MIN: parts of this many strikes and more run quartic_kernel_dense_smc
     int layout = 0;            // BCU_LAYOUT: 0 = the three-kernel round (default), 1 = fused step kernel (bcu_step.cuh: bit-exact,
                                // measured 3-4 x slower: groups of lanes per strike leave most lanes idle), 2 = merged round
                                // kernel (bcu_round.cuh: apply folded into items, two kernels per round)

@@ -44,9 +44,13 @@ constexpr int QUARTIC_BLOCK = 128;
 #ifndef QUARTIC_MIN_BLOCKS
 #define QUARTIC_MIN_BLOCKS 6
 #endif
-#ifndef QUARTIC_DENSE_MIN_BLOCKS
-#define QUARTIC_DENSE_MIN_BLOCKS 10   // quartic_kernel_dense: the instantiation for large parts (see launch_pipeline)
+#ifndef QUARTIC_WIDE_BLOCK_V
+#define QUARTIC_WIDE_BLOCK_V 512      // quartic_kernel_wide: the kernel for large parts (see launch_pipeline)
 #endif
+#ifndef QUARTIC_WIDE_MIN_BLOCKS
+#define QUARTIC_WIDE_MIN_BLOCKS 2
+#endif
+constexpr int QUARTIC_WIDE_BLOCK = QUARTIC_WIDE_BLOCK_V;
 constexpr int APPLY_BLOCK = 256;
 
 enum Category : uint32_t { CAT_REST = 0, CAT_ROLLING = 1, CAT_STATIC_PAIR = 2, CAT_DYNAMIC_PAIR = 3, CAT_RAIL = 4, CAT_POCKET = 5 };
@@ -230,31 +234,26 @@ __global__ void __launch_bounds__(256) init_kernel(const LaunchParams* __restric
 // ---------------------------------------------------------------------------------------------------------------------
 // quartic: one thread per job.
 // ---------------------------------------------------------------------------------------------------------------------
-// -DQUARTIC_SORT_JOBS=1: AN EXPERIMENT THAT IS KEPT, NOT THE DEFAULT.  Measured (profiles/r02_ab_experiments.txt): 3.5 % SLOWER on
-// a large launch (95.4 against 98.9 M strikes/s) and 3 % slower on the 65 536-strike level -- the classification and the exchange
-// are paid per job and two of a CTA's four warps stay mixed.  The same idea on the PRODUCER's side won: items_kernel fills the
-// queue from both ends by class (JOB_SPLIT, bcu_items.cuh), which costs the consumer nothing.
-#ifndef QUARTIC_SORT_JOBS
-#define QUARTIC_SORT_JOBS 0
-#endif
-#ifndef QUARTIC_REAL_EIGHTHS
-#define QUARTIC_REAL_EIGHTHS 4
-#endif
-// Which arm of the solver a job will take: std::pow(complex, double) is a real pow() when its base is a positive real and
-// clog + exp + sincos otherwise (c_pow_real), and everything downstream (csqrt of real against complex values, the complex
-// divisions) follows that split -- two long, disjoint instruction streams that a warp with jobs of both kinds runs one after
-// the other.  The base is (deltaOne + sqrt(deltaOne^2 - 4 deltaZero^3)) / 2 of solve_quartic_roots, a few operations on the
-// coefficients.  A scheduling hint only: computed in plain double (no libm restatement); a wrong guess near a boundary costs
-// divergence and nothing else.
-__device__ __forceinline__ int quartic_job_class(const float co[5]) {
-    const double a = co[0], b = co[1], c = co[2], d = co[3], e = co[4];
-    const double dz = (c * c) - (3 * b * d) + (12 * a * e);
-    const double d1 = (2 * c * c * c) - (9 * b * c * d) + (27 * b * b * e) + (27 * a * d * d) - (72 * a * c * e);
-    const double R = d1 * d1 - 4.0 * dz * dz * dz;
-    if (!(R >= 0.0)) return 1;                 // complex base (three distinct real roots of the resolvent cubic)
-    return d1 + sqrt(R) > 0.0 ? 0 : 2;         // positive real base : negative real base
+// The job queue is filled from both ends by items_kernel (bcu_items.cuh stage 2): "real" jobs -- the solver's std::pow(complex,
+// double) takes its real arm -- from slot 0 upwards, "complex" jobs from the last slot downwards.  A job is its five coefficients
+// and its code, and its result reaches the strike's key through an atomicMin, so it does not matter which thread solves it.
+struct JobQueue {
+    uint64_t nFront, nBack;   // jobs in [0, nFront) and in (jobCap - 1 - nBack, jobCap - 1]
+};
+__device__ __forceinline__ JobQueue job_queue(const PipeWorkspace& w, int round) {
+    const uint32_t postedFront = w.counts[4 * round + 2], postedBack = w.counts[4 * round + 3];
+    JobQueue q;
+    q.nFront = postedFront < w.jobCap ? postedFront : w.jobCap;
+    q.nBack = postedBack < w.jobCap - q.nFront ? postedBack : w.jobCap - q.nFront;
+    if ((uint64_t)postedFront + postedBack > w.jobCap && blockIdx.x == 0 && threadIdx.x == 0)
+        w.counts[4 * ROUNDS + 3] = 1u;   // the two ends met: the host grows the queue and re-runs the launch
+    return q;
 }
-__device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsigned long long* key, const float co[5], uint32_t c2) {
+__device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsigned long long* key, uint64_t j) {
+    float co[5];
+    #pragma unroll
+    for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
+    const uint32_t c2 = w.jobCode[j];
     float t;
     if (collision_time_from_coefficients(co, &t)) {
         const uint32_t ent = (c2 & ~JOB_MARK) >> 6;
@@ -267,162 +266,39 @@ __device__ __forceinline__ void quartic_solve_job(const PipeWorkspace& w, unsign
         offer(key + (ent >> 5), t, make_code(ent & 31u, (c2 & 32u) ? CAT_DYNAMIC_PAIR : CAT_STATIC_PAIR, c2 & 31u));
     }
 }
-template <bool SM_CLASS>
-__device__ __forceinline__ void quartic_body(const PipeWorkspace& w, int round, unsigned bid, unsigned nb, int pref, uint32_t ticket0) {
-    (void)pref; (void)ticket0; (void)nb;
-    // the queue is filled from both ends (bcu_items.cuh stage 2): nFront jobs from slot 0 upwards, nBack from the last slot downwards
-    const uint32_t postedFront = w.counts[4 * round + 2], postedBack = w.counts[4 * round + 3];
-    const uint64_t nFront = postedFront < w.jobCap ? postedFront : w.jobCap;
-    const uint64_t nBack = postedBack < w.jobCap - nFront ? postedBack : w.jobCap - nFront;
-    const uint64_t nJobs = nFront + nBack;
-    if ((uint64_t)postedFront + postedBack > w.jobCap && bid == 0 && threadIdx.x == 0)
-        w.counts[4 * ROUNDS + 3] = 1u;   // the two ends met: the host grows the queue and re-runs the launch
+
+// Small parts (below PipeLaunchCfg::denseMinQuartic strikes): 128 threads x 6 CTAs per SM, 80 registers, one job per thread
+// and trip -- the rounds of such a part are latency-bound and want fast threads.
+__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+    const JobQueue q = job_queue(w, round);
     unsigned long long* key = w.key + (w.fused ? (size_t)0 : (size_t)(round % 3) * w.n);
-#if QUARTIC_SORT_JOBS
-    // The jobs of a tile change hands before they are solved: the CTA partitions its 128 jobs by class through shared memory,
-    // so that at most two of its four warps hold jobs of more than one class.  A job is its five coefficients and its code, and
-    // its result goes to the strike's key with an atomicMin, so it does not matter which thread solves it.
-    constexpr int NCLS = 3, NW = QUARTIC_BLOCK / 32;
-    __shared__ float sCo[5][QUARTIC_BLOCK];
-    __shared__ uint32_t sCode[QUARTIC_BLOCK];
-    __shared__ uint32_t sCnt[NW][NCLS];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint64_t base = (uint64_t)bid * QUARTIC_BLOCK; base < nJobs; base += (uint64_t)nb * QUARTIC_BLOCK) {
-        const uint64_t v = base + threadIdx.x;
-        const bool have = v < nJobs;
-        const uint64_t j = v < nFront ? v : w.jobCap - 1u - (v - nFront);
-        float co[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-        uint32_t c2 = 0;
-        int cls = -1;
-        if (have) {
-            #pragma unroll
-            for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
-            c2 = w.jobCode[j];
-            cls = quartic_job_class(co);
-        }
-        uint32_t mine = 0, cnt[NCLS];
-        #pragma unroll
-        for (int k = 0; k < NCLS; ++k) {
-            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
-            cnt[k] = __popc(m);
-            if (cls == k) mine = m;
-        }
-        if (lane < NCLS) sCnt[warp][lane] = lane == 0 ? cnt[0] : lane == 1 ? cnt[1] : cnt[2];
-        __syncthreads();
-        uint32_t at = __popc(mine & ((1u << lane) - 1u)), total = 0;
-        #pragma unroll
-        for (int k = 0; k < NCLS; ++k) {
-            #pragma unroll
-            for (int v = 0; v < NW; ++v) {
-                const uint32_t c = sCnt[v][k];
-                total += c;
-                if (k < cls || (k == cls && v < warp)) at += c;
-            }
-        }
-        if (have) {
-            #pragma unroll
-            for (int q = 0; q < 5; ++q) sCo[q][at] = co[q];
-            sCode[at] = c2;
-        }
-        __syncthreads();
-        const bool work = threadIdx.x < total;
-        if (work) {
-            #pragma unroll
-            for (int q = 0; q < 5; ++q) co[q] = sCo[q][threadIdx.x];
-            c2 = sCode[threadIdx.x];
-        }
-        __syncthreads();   // the tile is in registers: the next trip may overwrite it
-        if (work) quartic_solve_job(w, key, co, c2);
-    }
-#else
-  if constexpr (SM_CLASS) {
-    // Every SM works on ONE class of jobs for as long as there are any: the solver's two arms are disjoint instruction streams
-    // (17 KB and 30 KB of the 39 KB a mixed SM walks through), the SM's instruction cache holds 32 KB, and with both classes
-    // resident quartic_kernel was bound by instruction fetch (sm__icc hit rate 73 %, `no instruction` the largest stall,
-    // profiles/r02_quartic_dense_big_round_ncu_full.txt).  A CTA prefers the class of its SM (preferredClass: by %smid), takes
-    // tiles of 128 jobs of that class by ticket -- its first ticket was drawn before the grid dependency, the next one is
-    // drawn before the current tile is solved, so the atomics' latency is never waited for -- and moves to the other class
-    // once its own is used up.
-    __shared__ uint32_t sNext;
-    const uint64_t nOf[2] = {nFront, nBack};
-    uint32_t* tickets = w.tickets + 2 * round;
-    int cls = pref;
-    uint32_t t = ticket0;
-    bool moved = false;
-    for (;;) {
-        if ((uint64_t)t * QUARTIC_BLOCK >= nOf[cls]) {
-            if (moved) break;
-            moved = true;
-            cls ^= 1;
-            if (nOf[cls] == 0) break;
-            __syncthreads();
-            if (threadIdx.x == 0) sNext = atomicAdd(&tickets[cls], 1u);
-            __syncthreads();
-            t = sNext;
-            continue;
-        }
-        uint32_t nxt = 0;
-        if (threadIdx.x == 0) nxt = atomicAdd(&tickets[cls], 1u);   // used after the solve
-        const uint64_t v = (uint64_t)t * QUARTIC_BLOCK + threadIdx.x;
-        if (v < nOf[cls]) {
-            const uint64_t j = cls == 0 ? v : w.jobCap - 1u - v;
-            float co[5];
-            #pragma unroll
-            for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
-            quartic_solve_job(w, key, co, w.jobCode[j]);
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) sNext = nxt;
-        __syncthreads();
-        t = sNext;
-    }
-  } else {
-    for (uint64_t v = (uint64_t)bid * QUARTIC_BLOCK + threadIdx.x; v < nJobs; v += (uint64_t)nb * QUARTIC_BLOCK) {
-        const uint64_t j = v < nFront ? v : w.jobCap - 1u - (v - nFront);
-        float co[5];
-        #pragma unroll
-        for (int q = 0; q < 5; ++q) co[q] = w.jobCo[(size_t)q * w.jobCap + j];
-        quartic_solve_job(w, key, co, w.jobCode[j]);
-    }
-  }
-#endif
+    const uint64_t nJobs = q.nFront + q.nBack;
+    for (uint64_t v = (uint64_t)blockIdx.x * QUARTIC_BLOCK + threadIdx.x; v < nJobs; v += (uint64_t)gridDim.x * QUARTIC_BLOCK)
+        quartic_solve_job(w, key, v < q.nFront ? v : w.jobCap - 1u - (v - q.nFront));
 }
 
-// class an SM prefers: QUARTIC_REAL_EIGHTHS of every 8 SMs take the "real" jobs (front of the queue), the others the "complex" ones
-__device__ __forceinline__ int preferredClass() {
-    unsigned smid;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    return (smid & 7u) < (unsigned)QUARTIC_REAL_EIGHTHS ? 0 : 1;
-}
-template <bool SM_CLASS>
-__device__ __forceinline__ void quartic_entry(const PipeWorkspace& w, int round) {
-    if constexpr (SM_CLASS && !QUARTIC_SORT_JOBS) {
-        __shared__ uint32_t sFirst;
-        const int pref = preferredClass();
-        // the tickets are zeroed at the start of the launch and belong to this round's quartic kernel alone: nothing the
-        // previous kernel writes is read before the grid dependency
-        if (threadIdx.x == 0) sFirst = atomicAdd(&w.tickets[2 * round + pref], 1u);
-        if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-        cudaGridDependencySynchronize();
+// Large parts: the solver is bound by INSTRUCTION FETCH when the warps of an SM are spread over it -- a job walks through 39 KB
+// of code, the SM's instruction cache holds ~32 KB (sm__icc hit rate 73 %, `no instruction` the largest stall,
+// profiles/r02_big_round_instruction_fetch.txt).  Here the warps of a CTA start every tile of jobs TOGETHER (a barrier per
+// tile) and the tiles are of one class (front region first, then the back region; no tile straddles them), so the warps walk the
+// code side by side and need a few KB of it at any time: 512 threads x 2 CTAs per SM, 64 registers.  Measured against the same
+// kernel without the barrier and with 128-thread CTAs (profiles/r02_ab_experiments.txt): 1000 tables x 4096 strikes 116.6 against
+// 105.1 M strikes/s (81.9 against 72.6 M with the reach bound off); parts of 2^18 strikes 120 against 110 M.
+__global__ void __launch_bounds__(QUARTIC_WIDE_BLOCK, QUARTIC_WIDE_MIN_BLOCKS) quartic_kernel_wide(PipeWorkspace w, int round) {
+    if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+    const JobQueue q = job_queue(w, round);
+    unsigned long long* key = w.key + (w.fused ? (size_t)0 : (size_t)(round % 3) * w.n);
+    const uint64_t tilesFront = (q.nFront + QUARTIC_WIDE_BLOCK - 1) / QUARTIC_WIDE_BLOCK;
+    const uint64_t tilesBack = (q.nBack + QUARTIC_WIDE_BLOCK - 1) / QUARTIC_WIDE_BLOCK;
+    for (uint64_t t = blockIdx.x; t < tilesFront + tilesBack; t += gridDim.x) {
         __syncthreads();
-        quartic_body<true>(w, round, blockIdx.x, gridDim.x, pref, sFirst);
-    } else {
-        if (w.pdlEarly) cudaTriggerProgrammaticLaunchCompletion();
-        cudaGridDependencySynchronize();
-        quartic_body<false>(w, round, blockIdx.x, gridDim.x, 0, 0u);
+        const bool front = t < tilesFront;
+        const uint64_t v = (front ? t : t - tilesFront) * QUARTIC_WIDE_BLOCK + threadIdx.x;
+        if (v < (front ? q.nFront : q.nBack)) quartic_solve_job(w, key, front ? v : w.jobCap - 1u - v);
     }
-}
-// Three instantiations (launch_pipeline chooses by the size of the part): the default one, the one compiled for more resident
-// CTAs per SM, and that one with the per-SM job classes.  Measured (profiles/r02_ab_experiments.txt): the tickets pay only on the
-// largest parts -- 1000 tables x 4096 strikes (parts of 2^20) 107.6 against 105.6 M strikes/s, 74.6 against 71.6 M exact; parts
-// of 2^19 the same either way; parts of 2^16 .. 2^18 LOSE 5-17 %, and the 65 536-strike level loses 8-10 % (its rounds are
-// latency-bound: a barrier per tile and, when a CTA changes class, an atomic round trip that is waited for).
-__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_MIN_BLOCKS) quartic_kernel(PipeWorkspace w, int round) { quartic_entry<false>(w, round); }
-__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_DENSE_MIN_BLOCKS) quartic_kernel_dense(PipeWorkspace w, int round) {
-    quartic_entry<false>(w, round);
-}
-__global__ void __launch_bounds__(QUARTIC_BLOCK, QUARTIC_DENSE_MIN_BLOCKS) quartic_kernel_dense_smc(PipeWorkspace w, int round) {
-    quartic_entry<true>(w, round);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -748,7 +624,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
     const size_t oStop = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oLive = take((size_t)2 * n * sizeof(uint32_t));
     const size_t oDyn = take((size_t)2 * w.dynCap * sizeof(uint32_t));
-    const size_t oCounts = take((size_t)(2 + 4) * (ROUNDS + 1) * sizeof(uint32_t));   // tickets [rounds + 1][2], then counts
+    const size_t oCounts = take((size_t)4 * (ROUNDS + 1) * sizeof(uint32_t));
     const size_t oCo = take((size_t)5 * w.jobCap * sizeof(float)), oCode = take(w.jobCap * sizeof(uint32_t));
     if (layout) {
         unsigned char* b = reinterpret_cast<unsigned char*>(layout->base);
@@ -759,8 +635,7 @@ size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWo
         w.key = reinterpret_cast<unsigned long long*>(b + oKey); w.T = reinterpret_cast<float*>(b + oT);
         w.dynMask = reinterpret_cast<uint32_t*>(b + oDm); w.restMask = reinterpret_cast<uint32_t*>(b + oRm);
         w.live = reinterpret_cast<uint32_t*>(b + oLive); w.dyn = reinterpret_cast<uint32_t*>(b + oDyn);
-        w.tickets = reinterpret_cast<uint32_t*>(b + oCounts);
-        w.counts = w.tickets + 2 * (ROUNDS + 1);
+        w.counts = reinterpret_cast<uint32_t*>(b + oCounts);
         w.jobCo = reinterpret_cast<float*>(b + oCo); w.jobCode = reinterpret_cast<uint32_t*>(b + oCode);
         w.buf[0] = StateBuf{w.pos, w.vel, w.vn, w.acc, w.nextRolling, w.meta};
         w.buf[1] = StateBuf{reinterpret_cast<float2*>(b + oPos2), reinterpret_cast<float2*>(b + oVel2), reinterpret_cast<float2*>(b + oVn2),
@@ -787,7 +662,7 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     if ((e = cudaMemsetAsync(w.key, 0xff, (size_t)3 * w.n * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     // the overflow flag is the last word of counts[]: sticky across the parts that share this workspace
     const size_t countWords = (size_t)4 * (ROUNDS + 1) - (resetOverflow ? 0 : 1);
-    if ((e = cudaMemsetAsync(w.tickets, 0, ((size_t)2 * (ROUNDS + 1) + countWords) * sizeof(uint32_t), stream)) != cudaSuccess) return e;   // tickets + counts
+    if ((e = cudaMemsetAsync(w.counts, 0, countWords * sizeof(uint32_t), stream)) != cudaSuccess) return e;
     const size_t itemSmem = (size_t)ITEM_BLOCK * (2 * nBalls) * sizeof(uint16_t);
     (void)nRails; (void)nPockets;
     const int64_t initBlocks = (w.n + 255) / 256, finBlocks = (w.n + 7) / 8;
@@ -818,9 +693,9 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
         if (occQuartic < 1) occQuartic = 1;
         if (occApply < 1) occApply = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occItemsDense, items_kernel_dense, ITEM_BLOCK, itemSmem);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occQuarticDense, quartic_kernel_dense, QUARTIC_BLOCK, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cfg.occQuarticWide, quartic_kernel_wide, QUARTIC_WIDE_BLOCK, 0);
         if (cfg.occItemsDense < 1) cfg.occItemsDense = 1;
-        if (cfg.occQuarticDense < 1) cfg.occQuarticDense = 1;
+        if (cfg.occQuarticWide < 1) cfg.occQuarticWide = 1;
         occSmem = itemSmem;
     }
     // Programmatic dependent launch: every kernel after init is launched with the stream-serialisation attribute and signals
@@ -871,18 +746,18 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
             mark();
         }
     }
-    // Parts of 65 536 strikes and more (cfg.denseMinItems / denseMinQuartic) take the instantiations of items / quartic that
-    // are compiled for more resident CTAs per SM.  Measured (profiles/r02_dense_sweep.txt): 1000 tables x 4096 strikes (parts
-    // of 2^20) 99.1 M strikes/s against 93.7 M, parts of 131 072: 96.7 against 91.3; parts of 65 536: -1 % with the reach bound,
-    // +6 % without; parts of 32 768 (the 65 536-strike level, latency-bound rounds) lose 3-5 % with them.  Same code, same results.
+    // Parts of 65 536 strikes and more (cfg.denseMinItems / denseMinQuartic) take the kernels for large parts: items_kernel_dense
+    // (the same body compiled for more resident CTAs per SM) and quartic_kernel_wide (CTAs whose warps walk the solver side by
+    // side).  Measured (profiles/r02_dense_sweep.txt, profiles/r02_ab_experiments.txt): 1000 tables x 4096 strikes (parts of 2^20)
+    // 116.6 M strikes/s against 93.7 M with the small-part kernels; parts of 65 536: +2-4 %; parts of 32 768 (the 65 536-strike
+    // level, latency-bound rounds) lose 1-5 % with them.  Same code, same results.
     const bool denseI = w.n >= cfg.denseMinItems, denseQ = w.n >= cfg.denseMinQuartic;
-    const bool smClass = denseQ && w.n >= cfg.smClassMin;   // quartic_kernel_dense_smc: every SM works on one class of jobs
     for (int r = 0; r < ROUNDS && !w.fused && !w.merged; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * (denseI ? cfg.occItemsDense : occItems), ITEM_BLOCK, itemSmem);
         if ((e = cudaLaunchKernelEx(&ci, denseI ? items_kernel_dense : items_kernel, p, w, r)) != cudaSuccess) return e;
         mark();
-        cudaLaunchConfig_t cq = cfgOf(sms * (denseQ ? cfg.occQuarticDense : occQuartic), QUARTIC_BLOCK, 0);
-        if ((e = cudaLaunchKernelEx(&cq, smClass ? quartic_kernel_dense_smc : denseQ ? quartic_kernel_dense : quartic_kernel, w, r)) != cudaSuccess) return e;
+        cudaLaunchConfig_t cq = denseQ ? cfgOf(sms * cfg.occQuarticWide, QUARTIC_WIDE_BLOCK, 0) : cfgOf(sms * occQuartic, QUARTIC_BLOCK, 0);
+        if ((e = cudaLaunchKernelEx(&cq, denseQ ? quartic_kernel_wide : quartic_kernel, w, r)) != cudaSuccess) return e;
         mark();
         cudaLaunchConfig_t ca = cfgOf(sms * occApply, APPLY_BLOCK, 0);
         if ((e = cudaLaunchKernelEx(&ca, apply_kernel, p, w, r)) != cudaSuccess) return e;

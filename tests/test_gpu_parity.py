@@ -594,15 +594,15 @@ def test_experimental_round_layouts_are_bit_identical(engine, table, layout):
         other.close()
 
 
-@pytest.mark.parametrize("knobs", [{"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "1000000000"}, {"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "0"},
-                                   {"BCU_DENSE_MIN": "0", "BCU_SM_CLASS_MIN": "0", "BCU_JOBS_PER_STRIKE": "1"}],
-                         ids=["dense", "dense-sm-classes", "dense-sm-classes-queue-overflow"])
+@pytest.mark.parametrize("knobs", [{"BCU_DENSE_MIN": "0"}, {"BCU_DENSE_MIN": "0", "BCU_JOBS_PER_STRIKE": "1"},
+                                   {"BCU_DENSE_MIN_ITEMS": "0"}, {"BCU_DENSE_MIN_QUARTIC": "0"}],
+                         ids=["both", "both-queue-overflow", "items-only", "quartic-only"])
 def test_large_part_kernels_are_bit_identical(engine, table, knobs):
-    """launch_pipeline takes other instantiations of items / quartic for large parts (compiled for more resident CTAs per SM;
-    from 2^20 strikes on, every SM prefers one class of quartic jobs and takes tiles by ticket).  The thresholds are engine
-    settings read from the environment at bcu_create: an engine that uses those kernels on a SMALL launch must return exactly what
-    the default engine returns -- every output incl. the event log, both prune modes -- also when the two-ended job queue
-    overflows and the launch is repeated with a larger one."""
+    """launch_pipeline takes other kernels for large parts: items_kernel_dense (compiled for more resident CTAs per SM) and
+    quartic_kernel_wide (CTAs of 512 threads whose warps start every tile of jobs together; tiles of one job class).  The
+    thresholds are engine settings read from the environment at bcu_create: an engine that uses those kernels on a SMALL launch
+    must return exactly what the default engine returns -- every output incl. the event log, both prune modes -- also when the
+    two-ended job queue overflows and the launch is repeated with a larger one."""
     from billiard_ai_b200 import Engine, workloads as W
     pos, types = W.snooker22_open(33)
     dirs, speeds = W.grid(192, 24)
