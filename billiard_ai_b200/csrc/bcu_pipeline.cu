@@ -751,7 +751,9 @@ cudaError_t launch_pipeline(const LaunchParams* p, int nBalls, int nRails, int n
     // side).  Measured (profiles/r02_dense_sweep.txt, profiles/r02_ab_experiments.txt): 1000 tables x 4096 strikes (parts of 2^20)
     // 116.6 M strikes/s against 93.7 M with the small-part kernels; parts of 65 536: +2-4 %; parts of 32 768 (the 65 536-strike
     // level, latency-bound rounds) lose 1-5 % with them.  Same code, same results.
-    const bool denseI = w.n >= cfg.denseMinItems, denseQ = w.n >= cfg.denseMinQuartic;
+    // With the reach bound off a round has about twice the quartic jobs, and the wide kernel already pays on parts of 32 768
+    // strikes (the benched level: 31.2 M against 30.0 M strikes/s; with the bound on 40.5 against 40.7 M).
+    const bool denseI = w.n >= cfg.denseMinItems, denseQ = w.n >= (w.pruneMode == 1 ? cfg.denseMinQuartic : cfg.denseMinQuartic / 2);
     for (int r = 0; r < ROUNDS && !w.fused && !w.merged; ++r) {
         cudaLaunchConfig_t ci = cfgOf(sms * (denseI ? cfg.occItemsDense : occItems), ITEM_BLOCK, itemSmem);
         if ((e = cudaLaunchKernelEx(&ci, denseI ? items_kernel_dense : items_kernel, p, w, r)) != cudaSuccess) return e;
