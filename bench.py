@@ -443,6 +443,10 @@ def run_b200(args, rank, local_rank, world):
                 "fractions_note": "executed = quartics this build solves x measured FP64 FLOP per quartic; algorithmic = the "
                                   "reference's quartic count x the same (the reach bound skips the difference); issue slots = "
                                   "warp instructions of a level / (kernel ms x 592 issue slots per clock x SM clock)",
+                "limiter_note": "a 65 536-strike level is bound by its chain of 31 dependent rounds (a 256-strike level takes 60 % of "
+                                "its time), not by a pipe; at scale (extra.config5_slice) the path is issue-bound and the quartic "
+                                "solver was bound by instruction fetch until quartic_kernel_wide (sm__icc hit rate 73 -> 91 %, "
+                                "profiles/r02_big_round_instruction_fetch.txt; DESIGN.md section 4)",
                 "fp64_flop_per_quartic": w_quartic, "fp64_flop_per_quartic_source": w_src,
                 "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "measured in this run: un-fused DADD+DMUL issue rate (FMA contraction is forbidden on "
