@@ -14,8 +14,9 @@
 //                   stages (rail / pocket quadratics, quantised quartic coefficients) run on dense threads.
 //                   Rail / pocket times go to the strike's 64-bit (time, evaluation order) key with atomicMin -- the
 //                   reference's strict-'<' first-evaluated-wins choice (:2002-2013); ball pairs become quartic jobs
-//                   in a global queue.
-//   quartic_kernel  one thread per job: the FP64 complex closed-form quartic (billiard_physics.cpp:470-560).
+//                   in a global queue, filled from both ends by the arm of the solver a job will take.
+//   quartic_kernel  one thread per job: the FP64 complex closed-form quartic (billiard_physics.cpp:470-560).  Large parts
+//                   take quartic_kernel_wide: CTAs whose warps walk the solver side by side (instruction cache).
 //   apply_kernel    one thread per live strike applies the winning event (createLayer :1957-1992, System::append
 //                   type.cpp:467-531) and one thread per other dynamic ball advances it in closed form; both
 //                   offer the rest / rolling times of the next round (nextBallInRest :1590, nextRolling :1575) and

@@ -1,4 +1,4 @@
-# GPU-box helper: one ncu --set full capture (with source) of quartic_kernel_dense on a LARGE round (128 tables x 4096 strikes in
+# GPU-box helper: one ncu --set full capture (with source) of the large-part quartic kernel (quartic_kernel_wide) on a LARGE round (128 tables x 4096 strikes in
 # one part, reach bound off, round 2) and the per-function / per-line breakdown of executed instructions and active lanes.
 cd $GRAFT_REPO_ROOT
 export BCU_NO_GRAPH=1 BCU_STREAMS=1

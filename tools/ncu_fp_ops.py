@@ -33,7 +33,7 @@ def main(path, counters_path, note):
     launches = collections.OrderedDict()
     for r in rows:
         name = re.sub(r"\(.*", "", r[ki]).replace("unnamed>::", "").split("::")[-1]
-        name = re.sub(r"_dense(_smc)?$", "", name)   # the instantiations for large parts: same code, other launch bounds
+        name = re.sub(r"_(dense|wide)$", "", name)   # the kernels for large parts: same work per item / job
         v = float(r[vi].replace(",", ""))
         if r[ui] == "ns":
             v /= 1e3

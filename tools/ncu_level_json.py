@@ -13,7 +13,7 @@ def main(path, note):
     launches = collections.OrderedDict()
     for r in rows:
         name = re.sub(r"\(.*", "", r[4]).replace("unnamed>::", "")
-        name = re.sub(r"_dense(_smc)?$", "", name)   # the instantiations for large parts: same code, other launch bounds
+        name = re.sub(r"_(dense|wide)$", "", name)   # the kernels for large parts: same work per item / job
         v = float(r[14].replace(",", ""))
         if r[13] == "ns":
             v /= 1e3                                                        # times in us
