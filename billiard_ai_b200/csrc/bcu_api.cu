@@ -279,6 +279,7 @@ int bcu_create(const bcu_table_desc* table, const bcu_rules_desc* rules, int dev
     cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, device);
     if (getenv("BCU_NO_GRAPH") || getenv("BCU_ROUND_TIMING")) e->useGraph = false;
     e->pipeCfg.roundTiming = getenv("BCU_ROUND_TIMING") != nullptr;
+    e->pipeCfg.quarticTwice = getenv("BCU_QUARTIC_TWICE") != nullptr;
     if (const char* pv = getenv("BCU_PDL")) e->pipeCfg.pdlMode = atoi(pv);
     if (const char* gv = getenv("BCU_GRID_PCT")) { const int v = atoi(gv); e->pipeCfg.gridPct = v < 5 ? 5 : v > 400 ? 400 : v; }
     if (const char* dv = getenv("BCU_DENSE_MIN")) { const long long v = atoll(dv); e->pipeCfg.denseMinItems = e->pipeCfg.denseMinQuartic = v < 0 ? 0 : v; }

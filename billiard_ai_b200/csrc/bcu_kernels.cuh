@@ -127,6 +127,7 @@ struct PipeLaunchCfg {
     int gridPct = 100;         // BCU_GRID_PCT (experiment): grids of the round kernels as a percentage of one resident wave
     int pdlMode = 1;           // BCU_PDL: 0 off, 1 programmatic dependent launch, 2 + early trigger
     bool roundTiming = false;  // BCU_ROUND_TIMING (diagnosis): CUDA events around every kernel, times on stderr
+    bool quarticTwice = false; // BCU_QUARTIC_TWICE (diagnosis, with BCU_ROUND_TIMING): every quartic kernel is launched a second time
 };
 size_t pipeline_workspace_bytes(int64_t n, int nBalls, int jobsPerStrike, PipeWorkspace* layout);
 const uint32_t* pipeline_overflow_flag(const PipeWorkspace& w);
